@@ -1,0 +1,121 @@
+// Shared declarations for the gprb200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include "../../include/gprb200.h"
+
+namespace gprb200 {
+
+constexpr int NB = 128;  // Cholesky diagonal-block size (one CTA factors NB x NB in shared memory)
+
+// Flat kernel program, passed by value to kernels (lives in constant bank / param space).
+struct KProg {
+    int nops;
+    int nparams;
+    int nper;  // number of PERIODIC leaves
+    int max_stack;
+    int8_t op[GPRB200_MAX_OPS];
+    int8_t poff[GPRB200_MAX_OPS];  // offset of the leaf's first parameter
+    double par[GPRB200_MAX_PARAMS];
+};
+
+struct GemmArgs {
+    const double* A;
+    const double* B;
+    double* C;
+    int64_t lda, ldb, ldc;
+    int M, N, K;
+    double alpha, beta;
+    int lower;  // 1: only tiles that intersect {row >= col} are computed (SYRK trailing update)
+};
+
+enum GemmForm { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    int64_t launches = 0;
+
+    KProg prog{};
+    bool have_kernel = false;
+
+    // training data (device)
+    int64_t N = 0, M = 0;
+    int d = 0;
+    double sigma = 0.0;
+    double* dX = nullptr;   // N x d (ld = d)
+    double* dY = nullptr;   // N x ldy
+    double* dA = nullptr;   // alpha, N x ldy
+    int64_t ldy = 0;
+    double* dL = nullptr;   // N x ldk: lower Cholesky factor of K + sigma^2 I (upper part: stale K)
+    int64_t ldk = 0;
+    double* dInvL = nullptr;  // ceil(N/NB) blocks of NB x NB: inverses of the diagonal blocks of L
+    double* dC = nullptr;     // N x ldk explicit core matrix (lazy)
+    int* dInfo = nullptr;
+    double* dScratch = nullptr;  // small reductions
+    size_t scratch_bytes = 0;
+
+    bool have_train = false, have_factor = false, have_alpha = false, have_core = false;
+    bool core_is_loaded = false;  // C installed by set_state (Load), no factor behind it
+    double logdet = 0.0;
+
+    int64_t opt_gram_lower_only = 1;
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double phase_ms[GPRB200_T_COUNT] = {0};
+};
+
+// error helpers -----------------------------------------------------------------------------
+int fail(Ctx* c, int code, const std::string& msg);
+#define GP_CUDA(c, expr)                                                                              \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess)                                                                        \
+            return gprb200::fail((c), -100 - (int)_e,                                                 \
+                                 std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + \
+                                     ":" + std::to_string(__LINE__) + ")");                           \
+    } while (0)
+#define GP_TRY(expr)                \
+    do {                            \
+        int _r = (expr);            \
+        if (_r != 0) return _r;     \
+    } while (0)
+
+static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// kernels / drivers (each returns 0 or an error code; all async on c->stream) -----------------
+// gram.cu
+int gram_build(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, double* out, int64_t ldo,
+               bool symmetric, bool lower_only, double diag_add);
+int dgram_build(Ctx* c, double* out /* (P*N) x N */, int64_t ldo);
+int check_finite(Ctx* c, const double* A, int64_t rows, int64_t cols, int64_t ld, bool lower_only, int* bad_host);
+// fused likelihood-gradient contraction: out[p] = sum_ij S_ij * dK_p(i,j), S symmetric N x N (lds)
+int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host /* P */);
+// dgemm.cu
+int gemm(Ctx* c, GemmForm form, const GemmArgs& g);
+// potrf.cu
+int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host);
+int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host);
+// solve.cu
+int trsm_lower_fwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,
+                   int64_t M);
+int trsm_lower_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,
+                   int64_t M);
+int inverse_from_factor(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* C, int64_t ldc);
+// util kernels (util.cu)
+int copy2d(Ctx* c, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t rows, int64_t cols);
+int fill2d(Ctx* c, double* dst, int64_t ldd, int64_t rows, int64_t cols, double v);
+int set_identity(Ctx* c, double* dst, int64_t ldd, int64_t n);
+int symmetrize_from_lower(Ctx* c, double* A, int64_t ld, int64_t n);
+int zero_upper(Ctx* c, double* A, int64_t ld, int64_t n);
+int coldot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, int64_t rows, int64_t cols,
+           double* d_out /* cols */);
+int rowdot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, int64_t rows, int64_t cols,
+           double* d_out /* rows */);
+// predict.cu
+int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out);
+
+}  // namespace gprb200

@@ -1,0 +1,258 @@
+// fp64 tensor-core GEMM for sm_100a: C = alpha * op(A) * op(B) + beta * C, everything row-major.
+//
+// This is the work-horse behind the blocked Cholesky (SYRK trailing update and the TRSM-as-GEMM
+// panel solve), the triangular solves for alpha = (K + sigma^2 I)^-1 Y and batched prediction.
+// It replaces the reference's LAPACK / Eigen products (include/LAPACKUtils.h:46-50,
+// lib/GaussianProcess.cpp:661, :60).
+//
+// Hardware mapping (measured on B200, profiles/r01_fp64_probe.txt): every f64 mma.sync shape
+// lowers to DMMA.8x8x4, which issues at 37.1 TFLOP/s chip-wide (128 flop/clk/SM @ 1.965 GHz);
+// tcgen05 has no f64 kind, so this warp-level path IS the FP64 tensor path on sm_100a.
+// One warp owns a 64x32 accumulator tile (8x4 DMMA atoms, 64 doubles/thread); per k4 step it
+// loads 8 A + 4 B fragments (12 LDS.64) for 32 DMMAs, i.e. shared-memory traffic is ~20 % of the
+// crossbar while the tensor pipe is saturated.
+//
+// Operand forms (K = contraction index):
+//   NT: A is M x K (k contiguous), B is N x K (k contiguous)        C = A B^T   (SYRK, panel solve)
+//   NN: A is M x K (k contiguous), B is K x N (n contiguous)        C = A B     (forward solve, predict)
+//   TN: A is K x M (m contiguous), B is K x N (n contiguous)        C = A^T B   (backward solve)
+// Global->shared: 16-byte cp.async (LDGSTS) with zero-fill for ragged edges, STAGES-deep ring.
+// k-contiguous tiles are stored [row][16] with the 16-byte chunk index XOR-swizzled by (row & 7)
+// (the TMA SWIZZLE_128B pattern), so the 8x4 fragment read is 2 wavefronts = the 256-byte minimum.
+// m/n-contiguous tiles are stored [16][rows + 8]: rows t and t+1 of a fragment land in opposite
+// 16-bank halves.
+#include "common.cuh"
+
+namespace gprb200 {
+
+constexpr int BK = 16;
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// tile geometry helpers ------------------------------------------------------------------------
+template <int ROWS, bool KC>
+struct OperandTile {
+    static constexpr int LD = KC ? BK : (ROWS + 8);
+    static constexpr int ELEMS = KC ? ROWS * BK : BK * (ROWS + 8);
+    // element (r = row in tile, k = 0..15)
+    __device__ static __forceinline__ int idx(int r, int k) {
+        if (KC) return r * BK + ((((k >> 1) ^ (r & 7)) << 1) | (k & 1));
+        return k * LD + r;
+    }
+    // cooperative async load of one k-tile. base points at the operand's (row 0, k 0) element.
+    // rows_valid / k_valid: remaining extent from the tile origin (may be <= 0 or > tile size).
+    template <int THREADS>
+    __device__ static __forceinline__ void load(double* tile, const double* base, int64_t ld, int rows_valid,
+                                                int k_valid, int tid) {
+        if (KC) {
+            constexpr int CHUNKS = ROWS * (BK / 2);
+#pragma unroll
+            for (int c = tid; c < CHUNKS; c += THREADS) {
+                const int r = c >> 3, ch = c & 7;
+                const int k = ch * 2;
+                int bytes = 0;
+                if (r < rows_valid) bytes = min(max((k_valid - k) * 8, 0), 16);
+                const double* src = bytes ? (base + (int64_t)r * ld + k) : base;
+                cp_async16(tile + r * BK + ((ch ^ (r & 7)) << 1), src, bytes);
+            }
+        } else {
+            constexpr int CPR = ROWS / 2;  // chunks per k-row
+            constexpr int CHUNKS = BK * CPR;
+#pragma unroll
+            for (int c = tid; c < CHUNKS; c += THREADS) {
+                const int k = c / CPR, ch = c - k * CPR;
+                const int r = ch * 2;
+                int bytes = 0;
+                if (k < k_valid) bytes = min(max((rows_valid - r) * 8, 0), 16);
+                const double* src = bytes ? (base + (int64_t)k * ld + r) : base;
+                cp_async16(tile + k * LD + r, src, bytes);
+            }
+        }
+    }
+};
+
+// linear block index -> (ti, tj). lower: row-tile ti has tiles tj = 0 .. last(ti), where
+// last(ti) = min(tiles_n - 1, (ti*BM + BM - 1) / BN).
+template <int BM, int BN>
+__device__ __forceinline__ void map_tile(int lin, int lower, int tiles_n, int& ti, int& tj) {
+    if (!lower) {
+        ti = lin / tiles_n;
+        tj = lin - ti * tiles_n;
+        return;
+    }
+    constexpr int R = BM / BN;  // BM is a multiple of BN; row-tile ti owns R*(ti+1) column tiles (before clamping)
+    // unclamped prefix: R * ti (ti + 1) / 2
+    int t = (int)((sqrt(1.0 + 8.0 * (double)lin / R) - 1.0) * 0.5);
+    while ((int64_t)R * (t + 1) * (t + 2) / 2 <= lin) ++t;
+    while ((int64_t)R * t * (t + 1) / 2 > lin) --t;
+    ti = t;
+    tj = lin - (int)((int64_t)R * t * (t + 1) / 2);
+}
+
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB>
+__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel(GemmArgs g, int tiles_n) {
+    constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
+    constexpr int WARPS_N = BN / WN;
+    constexpr int FM = WM / 8, FN = WN / 8;
+    using TA = OperandTile<BM, AKC>;
+    using TB = OperandTile<BN, BKC>;
+    extern __shared__ __align__(128) double smem[];
+    double* sA = smem;
+    double* sB = smem + STAGES * TA::ELEMS;
+
+    int ti, tj;
+    map_tile<BM, BN>(blockIdx.x, g.lower, tiles_n, ti, tj);
+    const int m0 = ti * BM, n0 = tj * BN;
+    if (m0 >= g.M || n0 >= g.N) return;  // (cannot happen for the grids we launch; cheap guard)
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
+    const int grp = lane >> 2, t4 = lane & 3;
+
+    const double* Abase = AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0);
+    const double* Bbase = BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0);
+    const int mrem = g.M - m0, nrem = g.N - n0;
+    const int nk = (g.K + BK - 1) / BK;
+
+    auto issue = [&](int kt) {
+        const int buf = kt % STAGES;
+        const int k0 = kt * BK;
+        const double* a = AKC ? (Abase + k0) : (Abase + (int64_t)k0 * g.lda);
+        const double* b = BKC ? (Bbase + k0) : (Bbase + (int64_t)k0 * g.ldb);
+        TA::template load<THREADS>(sA + buf * TA::ELEMS, a, g.lda, mrem, g.K - k0, tid);
+        TB::template load<THREADS>(sB + buf * TB::ELEMS, b, g.ldb, nrem, g.K - k0, tid);
+    };
+
+    double acc[FM][FN][2];
+#pragma unroll
+    for (int i = 0; i < FM; ++i)
+#pragma unroll
+        for (int j = 0; j < FN; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+#pragma unroll
+    for (int s = 0; s < STAGES - 1; ++s) {
+        if (s < nk) issue(s);
+        cp_async_commit();
+    }
+
+    for (int kt = 0; kt < nk; ++kt) {
+        cp_async_wait<STAGES - 2>();
+        __syncthreads();
+        if (kt + STAGES - 1 < nk) issue(kt + STAGES - 1);
+        cp_async_commit();
+
+        const double* a_t = sA + (kt % STAGES) * TA::ELEMS;
+        const double* b_t = sB + (kt % STAGES) * TB::ELEMS;
+#pragma unroll
+        for (int kk = 0; kk < BK / 4; ++kk) {
+            double af[FM], bf[FN];
+#pragma unroll
+            for (int i = 0; i < FM; ++i) af[i] = a_t[TA::idx(wm0 + i * 8 + grp, kk * 4 + t4)];
+#pragma unroll
+            for (int j = 0; j < FN; ++j) bf[j] = b_t[TB::idx(wn0 + j * 8 + grp, kk * 4 + t4)];
+#pragma unroll
+            for (int i = 0; i < FM; ++i)
+#pragma unroll
+                for (int j = 0; j < FN; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+        }
+    }
+    cp_async_wait<0>();
+
+    // epilogue: each thread owns (row, col..col+1) pairs -> 16-byte accesses (ldc and col are even)
+    const bool has_beta = (g.beta != 0.0);
+#pragma unroll
+    for (int i = 0; i < FM; ++i) {
+        const int row = m0 + wm0 + i * 8 + grp;
+        if (row >= g.M) continue;
+        double* crow = g.C + (int64_t)row * g.ldc;
+#pragma unroll
+        for (int j = 0; j < FN; ++j) {
+            const int col = n0 + wn0 + j * 8 + t4 * 2;
+            if (col + 1 < g.N) {
+                double2 v = make_double2(g.alpha * acc[i][j][0], g.alpha * acc[i][j][1]);
+                double2* p = reinterpret_cast<double2*>(crow + col);
+                if (has_beta) {
+                    const double2 o = *p;
+                    v.x = fma(g.beta, o.x, v.x);
+                    v.y = fma(g.beta, o.y, v.y);
+                }
+                *p = v;
+            } else if (col < g.N) {
+                double v = g.alpha * acc[i][j][0];
+                if (has_beta) v = fma(g.beta, crow[col], v);
+                crow[col] = v;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB>
+static int launch(Ctx* c, const GemmArgs& g) {
+    using TA = OperandTile<BM, AKC>;
+    using TB = OperandTile<BN, BKC>;
+    constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
+    constexpr size_t SMEM = sizeof(double) * STAGES * (TA::ELEMS + TB::ELEMS);
+    auto kern = dgemm_kernel<BM, BN, WM, WN, AKC, BKC, STAGES, MINB>;
+    static bool configured = false;  // per-process, per-instantiation
+    if (!configured) {
+        GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+        configured = true;
+    }
+    const int64_t tm = (g.M + BM - 1) / BM, tn = (g.N + BN - 1) / BN;
+    int64_t grid;
+    if (g.lower) {
+        constexpr int R = BM / BN;
+        grid = 0;
+        // row-tile ti owns min(tn, R*(ti+1)) tiles; the kernel's closed form assumes no clamping,
+        // which holds because the trailing matrix is square (M == N).
+        grid = (int64_t)R * tm * (tm + 1) / 2;
+    } else {
+        grid = tm * tn;
+    }
+    if (grid <= 0) return 0;
+    kern<<<(unsigned)grid, THREADS, SMEM, c->stream>>>(g, (int)tn);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    return 0;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+int gemm(Ctx* c, GemmForm form, const GemmArgs& g) {
+    if (g.M <= 0 || g.N <= 0) return 0;
+    if (!aligned16(g.A) || !aligned16(g.B) || !aligned16(g.C) || (g.lda & 1) || (g.ldb & 1) || (g.ldc & 1))
+        return fail(c, -2, "gemm: operands must be 16-byte aligned with even leading dimensions");
+    if (g.lower && g.M != g.N) return fail(c, -2, "gemm: lower-only update needs a square C");
+    // wide tile (128x128, 8 warps) when C has a single column tile that must be owned by one CTA
+    // (in-place panel solves), otherwise 128x64 tiles with two CTAs per SM so one CTA's epilogue
+    // overlaps the other's main loop.
+    const bool wide = (g.N > 64 && g.N <= 128 && !g.lower);
+    switch (form) {
+        case GEMM_NT:
+            return wide ? launch<128, 128, 64, 32, true, true, 3, 1>(c, g)
+                        : launch<128, 64, 64, 32, true, true, 4, 2>(c, g);
+        case GEMM_NN:
+            return wide ? launch<128, 128, 64, 32, true, false, 3, 1>(c, g)
+                        : launch<128, 64, 64, 32, true, false, 4, 2>(c, g);
+        case GEMM_TN:
+            return wide ? launch<128, 128, 64, 32, false, false, 3, 1>(c, g)
+                        : launch<128, 64, 64, 32, false, false, 4, 2>(c, g);
+    }
+    return fail(c, -2, "gemm: unknown form");
+}
+
+}  // namespace gprb200

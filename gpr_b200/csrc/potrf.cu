@@ -1,0 +1,154 @@
+// K3: right-looking blocked fp64 Cholesky, A = L L^T, lower, row-major, in place.
+// Replaces the reference's explicit LU inverse (include/LAPACKUtils.h:38-56, dgetrf+dgetri, 2 N^3
+// flop) and its Cholesky variant (:59-73, dpotrf+dpotri) as the core of InvertKernelMatrix
+// (lib/GaussianProcess.cpp:531-618): N^3/3 flop, and the factor is kept instead of the inverse.
+//
+// Per block step k (block size NB = 128):
+//   1. potrf_tile_kernel : one CTA factors the NB x NB diagonal block in shared memory and also
+//      forms inv(L_kk) (TRTRI) so that every triangular solve below becomes a GEMM;
+//   2. panel solve       : A[i,k] <- A[i,k] inv(L_kk)^T          (GEMM NT, in place, 1 % of flops)
+//   3. trailing update   : A[i,j] -= A[i,k] A[j,k]^T, i >= j > k (GEMM NT on lower tiles, 97 % of flops)
+// INFO follows LAPACK dpotrf: k > 0 = leading minor of order k is not positive definite.
+#include "common.cuh"
+#include <math.h>
+
+namespace gprb200 {
+
+constexpr int PT_THREADS = 512;
+constexpr int PT_LD = NB + 1;  // padded: column walks are conflict-free
+
+// A: n x n diagonal block (lda), n <= NB. invL: NB x NB row-major (ld NB) receives inv(L) (lower,
+// zero above the diagonal, zero-padded beyond n). info: set to col0 + j + 1 on the first failure.
+__global__ void __launch_bounds__(PT_THREADS, 1)
+potrf_tile_kernel(double* __restrict__ A, int64_t lda, int n, double* __restrict__ invL, int* info, int col0) {
+    extern __shared__ double sm[];
+    double* S = sm;                    // [NB][PT_LD]: strictly lower = L; upper incl. diagonal = inv(L)^T
+    double* diag = sm + NB * PT_LD;    // L_jj
+    double* colj = diag + NB;          // scaled column j
+    __shared__ int bad;
+    const int tid = threadIdx.x;
+    if (tid == 0) bad = 0;
+
+    for (int e = tid; e < n * n; e += PT_THREADS) {
+        const int r = e / n, c = e - r * n;
+        if (c <= r) S[r * PT_LD + c] = A[(int64_t)r * lda + c];
+    }
+    __syncthreads();
+
+    // ---- unblocked right-looking Cholesky on the lower triangle
+    const int tx = tid & 31, ty = tid >> 5;  // 32 x 16
+    for (int j = 0; j < n; ++j) {
+        const double ajj = S[j * PT_LD + j];
+        if (!(ajj > 0.0) || !isfinite(ajj)) {  // uniform across the CTA: everybody reads the same value
+            if (tid == 0) {
+                bad = 1;
+                atomicCAS(info, 0, col0 + j + 1);
+            }
+            break;
+        }
+        const double ljj = sqrt(ajj);
+        for (int i = j + 1 + tid; i < n; i += PT_THREADS) {
+            const double v = S[i * PT_LD + j] / ljj;
+            colj[i] = v;
+            S[i * PT_LD + j] = v;
+        }
+        if (tid == 0) diag[j] = ljj;
+        __syncthreads();
+        // rank-1 update of the trailing lower triangle
+        for (int i = j + 1 + ty; i < n; i += PT_THREADS / 32) {
+            const double li = colj[i];
+            for (int k = j + 1 + tx; k <= i; k += 32) S[i * PT_LD + k] = fma(-li, colj[k], S[i * PT_LD + k]);
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    if (bad) return;  // leave A untouched beyond this point; INFO tells the caller
+
+    // write L back (diagonal from diag[])
+    for (int e = tid; e < n * n; e += PT_THREADS) {
+        const int r = e / n, c = e - r * n;
+        if (c < r) A[(int64_t)r * lda + c] = S[r * PT_LD + c];
+        else if (c == r) A[(int64_t)r * lda + c] = diag[r];
+    }
+
+    // ---- X = inv(L), stored transposed in the upper triangle: X(i,c) lives at S[c][i], c <= i.
+    // Running right-hand side T starts as I; step j finalises row j of X and eliminates column j.
+    for (int e = tid; e < n * n; e += PT_THREADS) {
+        const int r = e / n, c = e - r * n;
+        if (c >= r) S[r * PT_LD + c] = (c == r) ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    for (int j = 0; j < n; ++j) {
+        const double ljj = diag[j];
+        for (int cidx = tid; cidx <= j; cidx += PT_THREADS) S[cidx * PT_LD + j] /= ljj;  // X(j, c)
+        __syncthreads();
+        // T(i, c) -= L(i, j) X(j, c) for i > j, c <= j
+        for (int i = j + 1 + ty; i < n; i += PT_THREADS / 32) {
+            const double lij = S[i * PT_LD + j];
+            for (int cidx = tx; cidx <= j; cidx += 32)
+                S[cidx * PT_LD + i] = fma(-lij, S[cidx * PT_LD + j], S[cidx * PT_LD + i]);
+        }
+        __syncthreads();
+    }
+    for (int e = tid; e < NB * NB; e += PT_THREADS) {
+        const int r = e / NB, c = e - r * NB;
+        invL[e] = (r < n && c <= r) ? S[c * PT_LD + r] : 0.0;
+    }
+}
+
+__global__ void logdet_kernel(const double* L, int64_t ld, int64_t n, double* out) {
+    // single CTA, fixed order: deterministic
+    __shared__ double red[32];
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) s += log(L[i * ld + i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        out[0] = 2.0 * t;
+    }
+}
+
+int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host) {
+    const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
+    GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
+    for (int64_t k0 = 0; k0 < N; k0 += NB) {
+        const int n = (int)((N - k0 < NB) ? (N - k0) : NB);
+        double* Akk = A + k0 * ld + k0;
+        double* invk = invL + (k0 / NB) * (int64_t)NB * NB;
+        potrf_tile_kernel<<<1, PT_THREADS, smem, c->stream>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+        ++c->launches;
+        GP_CUDA(c, cudaGetLastError());
+        const int64_t m = N - k0 - n;
+        if (m <= 0) break;
+        double* panel = A + (k0 + n) * ld + k0;
+        GemmArgs ps{};
+        ps.A = panel; ps.lda = ld; ps.B = invk; ps.ldb = NB; ps.C = panel; ps.ldc = ld;
+        ps.M = (int)m; ps.N = n; ps.K = n; ps.alpha = 1.0; ps.beta = 0.0; ps.lower = 0;
+        GP_TRY(gemm(c, GEMM_NT, ps));
+        GemmArgs tu{};
+        tu.A = panel; tu.lda = ld; tu.B = panel; tu.ldb = ld; tu.C = A + (k0 + n) * ld + (k0 + n); tu.ldc = ld;
+        tu.M = (int)m; tu.N = (int)m; tu.K = n; tu.alpha = -1.0; tu.beta = 1.0; tu.lower = 1;
+        GP_TRY(gemm(c, GEMM_NT, tu));
+    }
+    if (info_host) {
+        GP_CUDA(c, cudaMemcpyAsync(info_host, c->dInfo, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        GP_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return 0;
+}
+
+int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host) {
+    logdet_kernel<<<1, 1024, 0, c->stream>>>(L, ld, N, c->dScratch);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    GP_CUDA(c, cudaMemcpyAsync(out_host, c->dScratch, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    GP_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+}  // namespace gprb200

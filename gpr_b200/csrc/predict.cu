@@ -1,0 +1,104 @@
+// K6: prediction kernels.
+//   gemv_t : out[m] = sum_n kx[n] * A[n][m]  -- Predict for ONE test point, the call gpPredict makes per
+//            frame (reference lib/GaussianProcess.cpp:55-61, apps/GaussianProcessPredict.cpp:185-193).
+//            Reads all of alpha once: 8 N M bytes, purely HBM-bound (C2: 25.77 GB per prediction).
+// Layout: alpha is N x M row-major, so consecutive threads own consecutive output columns and every
+// warp-level load is a contiguous 512-byte run; each thread keeps UNROLL independent 16-byte loads
+// in flight. Rows are split across blockIdx.y so the grid is several waves of 148 SMs even when M
+// is small; partials are summed in a fixed order (deterministic).
+#include "common.cuh"
+
+namespace gprb200 {
+
+constexpr int GV_THREADS = 256;
+constexpr int GV_UNROLL = 8;
+
+__device__ __forceinline__ double2 ld_stream(const double2* p) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+
+// partial[split][m] = sum_{n in split} kx[n] A[n][m]; thread owns columns (2 c, 2 c + 1)
+__global__ void __launch_bounds__(GV_THREADS) gemv_t_kernel(const double* __restrict__ kx, const double* __restrict__ A,
+                                                             int64_t lda, int64_t N, int64_t M, int64_t rows_per_split,
+                                                             double* __restrict__ partial, int64_t ldp) {
+    extern __shared__ double skx[];
+    const int64_t n_begin = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t n_end = min(N, n_begin + rows_per_split);
+    for (int64_t i = threadIdx.x; i < n_end - n_begin; i += GV_THREADS) skx[i] = kx[n_begin + i];
+    __syncthreads();
+    const int64_t col = ((int64_t)blockIdx.x * GV_THREADS + threadIdx.x) * 2;
+    if (col >= M) return;
+    double s0 = 0.0, s1 = 0.0;
+    if (col + 1 < M) {
+        const double* base = A + col;
+        int64_t n = n_begin;
+        for (; n + GV_UNROLL <= n_end; n += GV_UNROLL) {
+            double2 v[GV_UNROLL];
+#pragma unroll
+            for (int u = 0; u < GV_UNROLL; ++u) v[u] = ld_stream(reinterpret_cast<const double2*>(base + (n + u) * lda));
+#pragma unroll
+            for (int u = 0; u < GV_UNROLL; ++u) {
+                const double k = skx[n - n_begin + u];
+                s0 = fma(k, v[u].x, s0);
+                s1 = fma(k, v[u].y, s1);
+            }
+        }
+        for (; n < n_end; ++n) {
+            const double2 v = ld_stream(reinterpret_cast<const double2*>(base + n * lda));
+            const double k = skx[n - n_begin];
+            s0 = fma(k, v.x, s0);
+            s1 = fma(k, v.y, s1);
+        }
+        partial[(int64_t)blockIdx.y * ldp + col] = s0;
+        partial[(int64_t)blockIdx.y * ldp + col + 1] = s1;
+    } else {
+        for (int64_t n = n_begin; n < n_end; ++n) s0 = fma(skx[n - n_begin], A[n * lda + col], s0);
+        partial[(int64_t)blockIdx.y * ldp + col] = s0;
+    }
+}
+
+__global__ void gemv_reduce_kernel(const double* partial, int64_t ldp, int splits, int64_t M, double* out) {
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    double s = 0.0;
+    for (int k = 0; k < splits; ++k) s += partial[(int64_t)k * ldp + m];
+    out[m] = s;
+}
+
+int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out) {
+    if (M <= 0) return 0;
+    const int64_t col_blocks = (M + 2 * GV_THREADS - 1) / (2 * GV_THREADS);
+    // aim for >= 8 waves of 148 SMs x 8 resident CTAs, but keep >= 256 rows per split
+    int64_t splits = (148 * 8 * 8 + col_blocks - 1) / col_blocks;
+    const int64_t max_splits = (N + 255) / 256;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    if (splits > 65535) splits = 65535;
+    int64_t rows_per_split = (N + splits - 1) / splits;
+    const int64_t cap_rows = 4096;  // shared-memory slice of kx: 32 KB
+    if (rows_per_split > cap_rows) rows_per_split = cap_rows;
+    splits = (N + rows_per_split - 1) / rows_per_split;
+    const int64_t ldp = round_up(M, 2);
+    const size_t need = sizeof(double) * splits * ldp;
+    double* partial = nullptr;
+    if (splits == 1) {
+        partial = out;
+    } else {
+        GP_CUDA(c, cudaMallocAsync(&partial, need, c->stream));
+    }
+    gemv_t_kernel<<<dim3((unsigned)col_blocks, (unsigned)splits), GV_THREADS, sizeof(double) * rows_per_split,
+                    c->stream>>>(kx, A, lda, N, M, rows_per_split, partial, splits == 1 ? 0 : ldp);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    if (splits > 1) {
+        gemv_reduce_kernel<<<(unsigned)((M + 255) / 256), 256, 0, c->stream>>>(partial, ldp, (int)splits, M, out);
+        ++c->launches;
+        GP_CUDA(c, cudaGetLastError());
+        GP_CUDA(c, cudaFreeAsync(partial, c->stream));
+    }
+    return 0;
+}
+
+}  // namespace gprb200

@@ -1,0 +1,157 @@
+/*
+ * gprb200.h — C-ABI of the B200-native GaussianProcess Learn/Predict hot path.
+ *
+ * This is the seam between the host C++ API (gpr::GaussianProcess<T>, gpr::Kernel<T>,
+ * gpr::GaussianLogLikelihood<T>; see gpr_b200/include/) and the hand-written sm_100a CUDA
+ * kernels in gpr_b200/csrc/.  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions
+ *   - all matrices are dense, ROW-MAJOR, IEEE fp64 (the reference's MatrixType is a row-major
+ *     Eigen matrix, reference include/GaussianProcess.h:41-46; its float instantiation casts to
+ *     double around LAPACK, reference include/LAPACKUtils.h:87,96);
+ *   - "host" entry points take host pointers and do the H2D/D2H copies themselves;
+ *     the *_dev entry points take DEVICE pointers (inputs already resident in HBM);
+ *   - every function returns 0 on success, >0 = LAPACK-style INFO ("leading minor of order k is
+ *     not positive definite"), <0 = argument / CUDA / NCCL error; gprb200_last_error() gives text.
+ *     The C++ wrapper rethrows as std::string, the reference's error convention
+ *     (reference lib/GaussianProcess.cpp:123,136,198,400,713).
+ *   - one handle == one GP model on one GPU; calls on one handle must be serialised by the
+ *     caller (the reference is not thread-safe either: include/GaussianProcess.h:164-165).
+ */
+#ifndef GPRB200_H
+#define GPRB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gprb200_ctx* gprb200_handle;
+
+/* Kernel "program": the kernel tree in post-order.  Leaves consume their parameters from the
+ * flat parameter vector in order; the parameter order is exactly Kernel::GetParameters() of the
+ * reference (k1's block first: include/Kernel.h:187-191).
+ *   GAUSSIAN      [sigma, scale]          include/Kernel.h:465-479
+ *   GAUSSIAN_EXP  [sigma, scale] (log)    include/Kernel.h:580-598
+ *   WHITE         [scale]                 include/Kernel.h:695-713
+ *   RQ            [scale, sigma, alpha]   include/Kernel.h:794-808
+ *   PERIODIC      [scale, b, sigma]       include/Kernel.h:912-948
+ *   SUM / PRODUCT pop two, push one       include/Kernel.h:165-178, 314-327            */
+enum gprb200_kernel_op {
+    GPRB200_K_GAUSSIAN = 1,
+    GPRB200_K_GAUSSIAN_EXP = 2,
+    GPRB200_K_WHITE = 3,
+    GPRB200_K_RQ = 4,
+    GPRB200_K_PERIODIC = 5,
+    GPRB200_K_SUM = 6,
+    GPRB200_K_PRODUCT = 7
+};
+#define GPRB200_MAX_OPS 32
+#define GPRB200_MAX_PARAMS 48
+#define GPRB200_MAX_STACK 8
+
+/* learn() flags */
+#define GPRB200_WANT_CORE 1u     /* also form C = inv(K + sigma^2 I) explicitly (for -CoreMatrix.txt) */
+
+/* loglik() modes */
+#define GPRB200_LOGLIK_REFERENCE_CLAMP 0 /* reproduce include/Likelihood.h:180-188 (det truncated to double, clamped) */
+#define GPRB200_LOGLIK_TRUE 1            /* cp = -0.5 * logdet from the Cholesky diagonal */
+
+/* phase timers (milliseconds, CUDA events on the handle's stream) */
+enum gprb200_phase {
+    GPRB200_T_GRAM = 0,
+    GPRB200_T_POTRF = 1,
+    GPRB200_T_SOLVE = 2,
+    GPRB200_T_INVERSE = 3,
+    GPRB200_T_PREDICT = 4,
+    GPRB200_T_DGRAM = 5,
+    GPRB200_T_LOGLIK = 6,
+    GPRB200_T_COUNT = 8
+};
+
+/* ---- lifetime -------------------------------------------------------------------------- */
+int gprb200_create(gprb200_handle* h, int device);
+int gprb200_destroy(gprb200_handle h);
+const char* gprb200_last_error(gprb200_handle h); /* h may be NULL: last create() error */
+const char* gprb200_version(void);
+/* Run all work of this handle on an existing cudaStream_t (e.g. torch's current stream). */
+int gprb200_set_stream(gprb200_handle h, void* cuda_stream);
+int gprb200_synchronize(gprb200_handle h);
+/* number of CUDA kernels this handle has launched since creation (bench.py's gpu_launches) */
+int64_t gprb200_launch_count(gprb200_handle h);
+int gprb200_phase_ms(gprb200_handle h, double* ms /* [GPRB200_T_COUNT] */);
+/* tuning knobs: "nb" (Cholesky block), "gram_lower_only" ... returns <0 for unknown names */
+int gprb200_set_option(gprb200_handle h, const char* name, int64_t value);
+
+/* ---- model definition ------------------------------------------------------------------ */
+/* replaces Kernel<T> virtual dispatch per matrix element (lib/GaussianProcess.cpp:392) */
+int gprb200_set_kernel(gprb200_handle h, const int32_t* ops, int nops, const double* params, int nparams);
+/* parameters only (hyper-parameter loop, include/GaussianProcessInference.h:90) */
+int gprb200_set_kernel_params(gprb200_handle h, const double* params, int nparams);
+
+/* replaces the AoS sample/label lists (lib/GaussianProcess.cpp:36-51) + ComputeLabelMatrix (:621-639)
+ * X: N x d, Y: N x M, sigma: observation noise (SetSigma). Copies; invalidates any factorisation. */
+int gprb200_set_train(gprb200_handle h, const double* X, int64_t N, int d, const double* Y, int64_t M, double sigma);
+int gprb200_set_train_dev(gprb200_handle h, const double* dX, int64_t N, int d, const double* dY, int64_t M,
+                          double sigma);
+int gprb200_set_sigma(gprb200_handle h, double sigma);
+
+/* Load path (lib/GaussianProcess.cpp:184-268): install alpha (N x M) and optionally the core
+ * matrix C (N x N, may be NULL = efficient storage) WITHOUT re-factorising (m_Initialized = true, :267). */
+int gprb200_set_state(gprb200_handle h, const double* X, int64_t N, int d, const double* Y /* may be NULL */,
+                      const double* alpha, int64_t M, const double* core /* may be NULL */, double sigma);
+
+/* ---- Learn ------------------------------------------------------------------------------- */
+/* ComputeKernelMatrix (+AddNoiseToKernelMatrix when add_noise): lib/GaussianProcess.cpp:363-402, 375-381.
+ * K_out: N x N host buffer (full symmetric). Returns -3 if K has non-finite entries (:399). */
+int gprb200_gram(gprb200_handle h, double* K_out, int add_noise);
+int gprb200_gram_dev(gprb200_handle h, double* dK_out, int64_t ldk, int add_noise);
+
+/* ComputeRegressionVectors (lib/GaussianProcess.cpp:642-672): Gram + sigma^2 I, Cholesky
+ * (replaces lu_invert, include/LAPACKUtils.h:38-56,85-97), alpha = (K + sigma^2 I)^-1 Y (:661). */
+int gprb200_learn(gprb200_handle h, unsigned flags);
+/* separately callable stages (bench / tests) */
+int gprb200_factorize(gprb200_handle h);        /* Gram + potrf only */
+int gprb200_solve_alpha(gprb200_handle h);      /* alpha from the current factor */
+
+int gprb200_get_alpha(gprb200_handle h, double* alpha /* N x M */);
+int gprb200_get_alpha_dev(gprb200_handle h, const double** d_alpha, int64_t* ld);
+/* C = inv(K + sigma^2 I), formed lazily from the factor (InvertKernelMatrix, lib/GaussianProcess.cpp:531-618) */
+int gprb200_get_core(gprb200_handle h, double* C /* N x N */);
+/* lower Cholesky factor L (row-major, strictly-upper part zeroed) */
+int gprb200_get_factor(gprb200_handle h, double* L /* N x N */);
+/* log det(K + sigma^2 I) = 2 sum log L_ii (replaces the long-double determinant, lib/GaussianProcess.cpp:527) */
+int gprb200_get_logdet(gprb200_handle h, double* logdet);
+
+/* ---- Predict ----------------------------------------------------------------------------- */
+/* Predict (lib/GaussianProcess.cpp:55-61) for T test points at once; T = 1 is the app's call.
+ * Xs: T x d.  mean: T x M.  ci (may be NULL): T values of GetCredibleInterval (:103-114),
+ * i.e. 2*sqrt(max(0, k(x,x) - Kx^T C Kx)). */
+int gprb200_predict(gprb200_handle h, const double* Xs, int64_t T, double* mean, double* ci);
+int gprb200_predict_dev(gprb200_handle h, const double* dXs, int64_t T, double* d_mean, int64_t ld_mean,
+                        double* d_ci);
+/* operator()(x,y) (lib/GaussianProcess.cpp:85-99): posterior covariance for T pairs (x_t, y_t). */
+int gprb200_posterior_cov(gprb200_handle h, const double* Xa, const double* Xb, int64_t T, double* cov);
+/* PredictDerivative (lib/GaussianProcess.cpp:65-81): mean (M) and D (d x M) = -Xd^T (Kx o alpha_i);
+ * no 1/sigma^2 factor, as in the reference. */
+int gprb200_predict_derivative(gprb200_handle h, const double* x, double* mean, double* D);
+/* ComputeKernelVector (lib/GaussianProcess.cpp:675-693) for T points: Kx is T x N */
+int gprb200_kernel_vector(gprb200_handle h, const double* Xs, int64_t T, double* Kx);
+
+/* ---- Likelihood -------------------------------------------------------------------------- */
+/* ComputeDerivativeKernelMatrix (lib/GaussianProcess.cpp:460-495): D is (P*N) x N, block p at rows [pN,(p+1)N). */
+int gprb200_dgram(gprb200_handle h, double* D_out);
+/* GaussianLogLikelihood (include/Likelihood.h:166-344). Re-factorises with the current kernel
+ * parameters (as the reference does on every call, :237), then
+ *   value[k] = -0.5 y_k^T C y_k + cp + ct                       (M values; may be NULL)
+ *   grad[p]  = 0.5 tr((alpha alpha^T - C) dK/dtheta_p)           (P values; may be NULL)  (:280-282)
+ *   jac[i,p] = 0.5 tr((alpha_i alpha_i^T - C) dK/dtheta_p)       (M x P;   may be NULL)  (:335-341) */
+int gprb200_loglik(gprb200_handle h, int mode, double* value, double* grad, double* jac);
+/* q[k] = y_k^T (K + sigma^2 I)^-1 y_k, the data-fit term of include/Likelihood.h:175 (M values) */
+int gprb200_quadform(gprb200_handle h, double* q);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPRB200_H */

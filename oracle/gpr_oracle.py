@@ -1,0 +1,296 @@
+"""CPU ORACLE (numpy/scipy) for the GaussianProcess Learn/Predict hot path of agiger/GPR.
+
+TEST INFRASTRUCTURE ONLY. Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this file; nothing under gpr_b200/ does.
+
+It restates the reference's algorithm function by function (citations are file:line under
+/root/reference) and calls the SAME LAPACK routines the reference calls for its default inversion
+path (dgetrf + dgetri, include/LAPACKUtils.h:38-56), through scipy.linalg.lapack.
+
+Parity status: pinned against (a) oracle/_ref — the reference's own Kernel.h / KernelFactory.h /
+lib/GaussianProcess.cpp / Likelihood.h compiled unmodified against an Eigen stand-in
+(tests/test_oracle_vs_ref.py, run in the build container where /root/reference exists), (b) the
+committed golden vectors generated from oracle/_ref (tests/golden/), and (c) the reference's own
+deterministic known-answer tests (tests/test_reference_known_answers.py).
+Third-party arithmetic not in /root/reference: Eigen 3 (README.md:63 names 3.2.4, unpinned by the
+build) for GEMM/GEMV/determinant; system LAPACK (unpinned) for dgetrf/dgetri/dpotrf/dpotri.
+"""
+import math
+
+import numpy as np
+from scipy.linalg import lapack
+
+LDBL_MIN = np.finfo(np.longdouble).tiny
+LDBL_MAX = np.finfo(np.longdouble).max
+
+
+# ------------------------------------------------------------------------------------------------
+# kernels (include/Kernel.h). A kernel is a nested tuple: (name, params...) or (name, k1, k2).
+# ------------------------------------------------------------------------------------------------
+def parse_kernel(s):
+    """KernelFactory::GetKernel (include/KernelFactory.h:83-178) for ToString()-style strings."""
+    s = s.strip()
+
+    def rec(pos):
+        lp = s.index("(", pos)
+        name = s[pos:lp].strip()
+        pos = lp + 1
+        if name in ("SumKernel", "ProductKernel"):
+            k1, pos = rec(pos)
+            while s[pos] in ", ":
+                pos += 1
+            k2, pos = rec(pos)
+            while s[pos] in ", ":
+                pos += 1
+            assert s[pos] == ")"
+            return (name, k1, k2), pos + 1
+        rp = s.index(")", pos)
+        vals = [float(t) for t in s[pos:rp].split(",") if t.strip()]
+        return (name,) + tuple(vals), rp + 1
+
+    return rec(0)[0]
+
+
+def num_params(k):
+    if k[0] in ("SumKernel", "ProductKernel"):
+        return num_params(k[1]) + num_params(k[2])
+    return len(k) - 1
+
+
+def get_params(k):
+    if k[0] in ("SumKernel", "ProductKernel"):
+        return get_params(k[1]) + get_params(k[2])
+    return list(k[1:])
+
+
+def set_params(k, p):
+    p = list(p)
+    if k[0] in ("SumKernel", "ProductKernel"):
+        n1 = num_params(k[1])
+        return (k[0], set_params(k[1], p[:n1]), set_params(k[2], p[n1:]))
+    return (k[0],) + tuple(p)
+
+
+def _pairwise_diff(A, B):
+    return A[:, None, :] - B[None, :, :]  # (na, nb, d)
+
+
+def kernel_matrix(k, A, B):
+    """k(a_i, b_j) for all pairs, vectorised restatement of the scalar functors."""
+    name = k[0]
+    if name == "SumKernel":  # include/Kernel.h:165-167
+        return kernel_matrix(k[1], A, B) + kernel_matrix(k[2], A, B)
+    if name == "ProductKernel":  # :314-316
+        return kernel_matrix(k[1], A, B) * kernel_matrix(k[2], A, B)
+    D = _pairwise_diff(A, B)
+    if name == "PeriodicKernel":  # :912-920, params [scale, b, sigma]
+        scale, b, sigma = k[1:]
+        s = np.sum(np.sin(b * D) ** 2, axis=2)
+        return scale * scale * np.exp(-0.5 * s / (sigma * sigma))
+    r = np.sqrt(np.sum(D * D, axis=2))  # (x-y).norm()
+    rr = r * r
+    if name == "GaussianKernel":  # :465-468, params [sigma, scale]
+        sigma, scale = k[1:]
+        return scale * scale * np.exp(-0.5 * rr / (sigma * sigma))
+    if name == "GaussianExpKernel":  # :580-585
+        sigma, scale = k[1:]
+        es, eg = math.exp(scale), math.exp(sigma)
+        return es * es * np.exp(-0.5 * rr / (eg * eg))
+    if name == "WhiteKernel":  # :695-702
+        (scale,) = k[1:]
+        return np.where(r == 0, scale * scale, 0.0)
+    if name == "RationalQuadraticKernel":  # :794-797, params [scale, sigma, alpha]
+        scale, sigma, alpha = k[1:]
+        return scale * scale * np.power(1 + 0.5 * rr / (sigma * sigma * alpha), -alpha)
+    raise ValueError(name)
+
+
+def kernel_derivative(k, A, B):
+    """Kernel::GetDerivative for all pairs -> array (P, na, nb)."""
+    name = k[0]
+    if name == "SumKernel":  # :169-178
+        return np.concatenate([kernel_derivative(k[1], A, B), kernel_derivative(k[2], A, B)], axis=0)
+    if name == "ProductKernel":  # :318-327
+        d1 = kernel_derivative(k[1], A, B) * kernel_matrix(k[2], A, B)[None]
+        d2 = kernel_derivative(k[2], A, B) * kernel_matrix(k[1], A, B)[None]
+        return np.concatenate([d1, d2], axis=0)
+    D = _pairwise_diff(A, B)
+    if name == "PeriodicKernel":  # :922-948
+        scale, b, sigma = k[1:]
+        f1 = np.sum(np.sin(b * D) ** 2, axis=2)
+        f2 = np.sum(2 * D * np.cos(b * D) * np.sin(b * D), axis=2)
+        e = np.exp(-0.5 * f1 / (sigma * sigma))
+        return np.stack([2 * scale * e, -0.5 * scale * scale * e * f2 / (sigma * sigma),
+                         scale * scale * e * f1 / (sigma ** 3)])
+    r = np.sqrt(np.sum(D * D, axis=2))
+    rr = r * r
+    if name == "GaussianKernel":  # :471-479
+        sigma, scale = k[1:]
+        f = np.exp(-0.5 * rr / (sigma * sigma))
+        return np.stack([scale * scale * rr / (sigma ** 3) * f, 2 * scale * f])
+    if name == "GaussianExpKernel":  # :588-598
+        sigma, scale = k[1:]
+        f1, f2 = math.exp(-2 * sigma), math.exp(2 * sigma)
+        return np.stack([rr * np.exp(-0.5 * f1 * ((4 * sigma - 4 * scale) * f2 + rr)),
+                         2 * np.exp(0.5 * f1 * (4 * f2 * scale - rr))])
+    if name == "WhiteKernel":  # :704-713
+        (scale,) = k[1:]
+        return np.where(r == 0, 2 * scale, 0.0)[None]
+    if name == "RationalQuadraticKernel":  # :799-808
+        scale, sigma, alpha = k[1:]
+        f = 0.5 * rr / (sigma * sigma * alpha) + 1
+        return np.stack([2 * scale * np.power(f, -alpha),
+                         scale * scale * rr * np.power(f, -alpha - 1) / sigma ** 3,
+                         scale * scale * ((rr / (2 * sigma * sigma * f * alpha)) - np.log(f)) * np.power(f, -alpha)])
+    raise ValueError(name)
+
+
+# ------------------------------------------------------------------------------------------------
+# dense algebra (include/LAPACKUtils.h)
+# ------------------------------------------------------------------------------------------------
+def lu_invert(K):
+    """lapack::lu_invert (include/LAPACKUtils.h:38-56, :85-97): dgetrf + dgetri on the row-major buffer
+    (LAPACK sees K^T; the inverse of the transpose is the transpose of the inverse, so the row-major
+    result is inv(K))."""
+    a = np.array(K.T, dtype=np.float64, order="F")  # row-major K viewed column-major == K^T
+    lu, piv, info = lapack.dgetrf(a, overwrite_a=True)
+    if info != 0:
+        raise np.linalg.LinAlgError("lu_invert: error in inversion. Matrix is singular or contains an illegal value.")
+    inv, info = lapack.dgetri(lu, piv, overwrite_lu=True)
+    if info != 0:
+        raise np.linalg.LinAlgError("lu_invert: error in inversion. Matrix is singular or contains an illegal value.")
+    return np.ascontiguousarray(inv.T)
+
+
+def chol_invert(K):
+    """lapack::chol_invert (include/LAPACKUtils.h:59-73, :100-111): dpotrf('L') + dpotri('L') on the
+    row-major buffer, then mirror the (row-major) upper triangle."""
+    a = np.array(K.T, dtype=np.float64, order="F")
+    c, info = lapack.dpotrf(a, lower=1, overwrite_a=True)
+    inv, info = lapack.dpotri(c, lower=1, overwrite_c=True)
+    rm = np.ascontiguousarray(inv.T)  # back to row-major indexing: A[i*N + j]
+    iu = np.triu_indices(rm.shape[0])
+    rm.T[iu] = rm[iu]  # A[j*N+i] = A[i*N+j] for j >= i
+    return rm
+
+
+# ------------------------------------------------------------------------------------------------
+# GaussianProcess (lib/GaussianProcess.cpp)
+# ------------------------------------------------------------------------------------------------
+class OracleGP:
+    def __init__(self, kernel, X, Y, sigma, inversion="lu"):
+        self.k = parse_kernel(kernel) if isinstance(kernel, str) else kernel
+        self.X = np.asarray(X, dtype=np.float64)
+        self.Y = np.asarray(Y, dtype=np.float64)
+        self.sigma = float(sigma)
+        self.inversion = inversion
+        self.C = None
+        self.alpha = None
+
+    # ComputeKernelMatrixInternal (:384-402): upper triangle evaluated, mirrored
+    def kernel_matrix(self):
+        K = kernel_matrix(self.k, self.X, self.X)
+        K = np.triu(K) + np.triu(K, 1).T
+        if not np.all(np.isfinite(K)):
+            raise FloatingPointError(
+                "GaussianProcess::ComputeKernelMatrixInternal: kernel matrix contains entries which are not finite.")
+        return K
+
+    # ComputeCoreMatrix (:498-510) with AddNoiseToKernelMatrix (:375-381) and InvertKernelMatrix (:531-618)
+    def core_matrix(self):
+        K = self.kernel_matrix()
+        K[np.diag_indices_from(K)] += self.sigma * self.sigma
+        self.Kn = K
+        return lu_invert(K) if self.inversion == "lu" else chol_invert(K)
+
+    # ComputeRegressionVectors (:642-672)
+    def learn(self):
+        self.C = self.core_matrix()
+        self.alpha = self.C @ self.Y  # :661
+        return self.alpha
+
+    def kernel_vector(self, x):  # :684-693
+        return kernel_matrix(self.k, np.atleast_2d(x), self.X)[0]
+
+    def predict(self, x):  # :55-61
+        return self.kernel_vector(x) @ self.alpha
+
+    def predict_batch(self, Xs):
+        return kernel_matrix(self.k, np.atleast_2d(Xs), self.X) @ self.alpha
+
+    def predict_derivative(self, x):  # :65-81, :697-706
+        x = np.asarray(x, dtype=np.float64).reshape(-1)
+        Kx = self.kernel_vector(x)
+        Xd = x[None, :] - self.X
+        D = np.stack([-Xd.T @ (Kx * self.alpha[:, i]) for i in range(self.alpha.shape[1])], axis=1)
+        return Kx @ self.alpha, D
+
+    def cov(self, x, y):  # operator() :85-99
+        Kx, Ky = self.kernel_vector(x), self.kernel_vector(y)
+        kxy = kernel_matrix(self.k, np.atleast_2d(x), np.atleast_2d(y))[0, 0]
+        return kxy - Kx @ self.C @ Ky
+
+    def credible_interval(self, x):  # :103-114
+        return 2.0 * math.sqrt(max(0.0, self.cov(x, x)))
+
+    def derivative_kernel_matrix(self):  # :472-495 -> (P*N, N)
+        D = kernel_derivative(self.k, self.X, self.X)
+        D = np.triu(D) + np.transpose(np.triu(D, 1), (0, 2, 1))
+        return D.reshape(-1, self.X.shape[0])
+
+    # ---- GaussianLogLikelihood (include/Likelihood.h:166-344) ------------------------------------
+    def _logdet(self):
+        # ComputeCoreMatrixWithDeterminant (:513-528) takes the long-double determinant by LU; the sign
+        # and log-magnitude from dgetrf pivots are the same quantity without the overflow.
+        lu, piv, info = lapack.dgetrf(np.array(self.Kn.T, order="F"))
+        d = np.diag(lu)
+        sign = np.prod(np.sign(d)) * (-1.0) ** np.sum(piv != np.arange(len(piv)))
+        return sign, np.sum(np.log(np.abs(d).astype(np.longdouble)))
+
+    def _cp(self, clamp=True):
+        sign, ld = self._logdet()
+        if not clamp:
+            return -0.5 * ld
+        with np.errstate(over="ignore", under="ignore"):
+            det = sign * np.exp(ld)          # long double
+            det = np.longdouble(np.float64(det))  # GetCoreMatrix returns TScalarType (:77-79)
+        if det <= LDBL_MIN:  # :180-188
+            return -0.5 * np.log(LDBL_MIN)
+        if det > LDBL_MAX:
+            return -0.5 * np.log(LDBL_MAX)
+        return -0.5 * np.log(det)
+
+    def loglik_value(self, clamp=True):
+        C = self.core_matrix()
+        N = C.shape[0]
+        df = -0.5 * np.einsum("nk,nm,mk->k", self.Y, C, self.Y)  # diagonal of -0.5 Y^T C Y (:175)
+        cp = self._cp(clamp)
+        ct = -N / 2.0 * math.log(2 * math.pi)  # :192
+        value = (df.astype(np.longdouble) + (cp + np.longdouble(ct))).astype(np.float64)
+        if np.isinf(value.sum()):
+            raise FloatingPointError(
+                "GaussianLogLikelihood::GetValueAndParameterDerivatives: likelihood is infinite.")
+        self.C = C
+        return value
+
+    def loglik_grad(self):  # :204-229 / :268-282: C subtracted ONCE for all output columns
+        C = self.core_matrix()
+        alpha = C @ self.Y
+        D = self.derivative_kernel_matrix()
+        N = C.shape[0]
+        P = D.shape[0] // N
+        A = alpha @ alpha.T - C
+        return np.array([0.5 * np.trace(A @ D[p * N:(p + 1) * N]) for p in range(P)])
+
+    def loglik_jacobian(self):  # :287-344
+        C = self.core_matrix()
+        D = self.derivative_kernel_matrix()
+        N = C.shape[0]
+        P = D.shape[0] // N
+        J = np.zeros((self.Y.shape[1], P))
+        for i in range(self.Y.shape[1]):
+            a = C @ self.Y[:, i:i + 1]
+            A = a @ a.T - C
+            for p in range(P):
+                J[i, p] = 0.5 * np.trace(A @ D[p * N:(p + 1) * N])
+        return J
