@@ -336,6 +336,12 @@ int gprb200_create(gprb200_handle* h, int device) {
         return -1;
     }
     c->own_stream = true;
+    {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        if (cudaStreamCreateWithPriority(&c->panel_stream, cudaStreamNonBlocking, hi) != cudaSuccess)
+            c->panel_stream = nullptr;  // look-ahead is then disabled
+    }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
         uint64_t thr = UINT64_MAX;
@@ -357,6 +363,7 @@ int gprb200_destroy(gprb200_handle h) {
     cudaFree(c->dInfo);
     cudaFree(c->dScratch);
     if (c->own_stream) cudaStreamDestroy(c->stream);
+    if (c->panel_stream) cudaStreamDestroy(c->panel_stream);
     delete c;
     return 0;
 }
@@ -390,10 +397,14 @@ int gprb200_phase_ms(gprb200_handle h, double* ms) {
 
 int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
-    if (!strcmp(name, "gram_lower_only")) {
-        h->opt_gram_lower_only = value;
-        return 0;
-    }
+    struct { const char* n; int64_t* p; } opts[] = {
+        {"gram_lower_only", &h->opt_gram_lower_only}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead},
+        {"gemm_stages", &h->opt_gemm_stages}, {"solve_left_min_m", &h->opt_solve_left_min_m}};
+    for (auto& o : opts)
+        if (!strcmp(name, o.n)) {
+            *o.p = value;
+            return 0;
+        }
     return fail(h, -2, std::string("set_option: unknown option '") + name + "'");
 }
 

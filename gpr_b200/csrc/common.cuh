@@ -63,6 +63,11 @@ struct Ctx {
     double logdet = 0.0;
 
     int64_t opt_gram_lower_only = 1;
+    int64_t opt_nbo = 1024;       // outer (trailing-update) block of the two-level Cholesky
+    int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs
+    int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
+    int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
+    cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double phase_ms[GPRB200_T_COUNT] = {0};
@@ -95,7 +100,7 @@ int check_finite(Ctx* c, const double* A, int64_t rows, int64_t cols, int64_t ld
 // fused likelihood-gradient contraction: out[p] = sum_ij S_ij * dK_p(i,j), S symmetric N x N (lds)
 int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host /* P */);
 // dgemm.cu
-int gemm(Ctx* c, GemmForm form, const GemmArgs& g);
+int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream = nullptr);
 // potrf.cu
 int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host);
 int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host);

@@ -201,17 +201,13 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
 
 // ---------------------------------------------------------------------------------------------
 template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB>
-static int launch(Ctx* c, const GemmArgs& g) {
+static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
     using TA = OperandTile<BM, AKC>;
     using TB = OperandTile<BN, BKC>;
     constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
     constexpr size_t SMEM = sizeof(double) * STAGES * (TA::ELEMS + TB::ELEMS);
     auto kern = dgemm_kernel<BM, BN, WM, WN, AKC, BKC, STAGES, MINB>;
-    static bool configured = false;  // per-process, per-instantiation
-    if (!configured) {
-        GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-        configured = true;
-    }
+    GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     const int64_t tm = (g.M + BM - 1) / BM, tn = (g.N + BN - 1) / BN;
     int64_t grid;
     if (g.lower) {
@@ -224,7 +220,7 @@ static int launch(Ctx* c, const GemmArgs& g) {
         grid = tm * tn;
     }
     if (grid <= 0) return 0;
-    kern<<<(unsigned)grid, THREADS, SMEM, c->stream>>>(g, (int)tn);
+    kern<<<(unsigned)grid, THREADS, SMEM, stream>>>(g, (int)tn);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     return 0;
@@ -232,8 +228,9 @@ static int launch(Ctx* c, const GemmArgs& g) {
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-int gemm(Ctx* c, GemmForm form, const GemmArgs& g) {
+int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     if (g.M <= 0 || g.N <= 0) return 0;
+    if (!stream) stream = c->stream;
     if (!aligned16(g.A) || !aligned16(g.B) || !aligned16(g.C) || (g.lda & 1) || (g.ldb & 1) || (g.ldc & 1))
         return fail(c, -2, "gemm: operands must be 16-byte aligned with even leading dimensions");
     if (g.lower && g.M != g.N) return fail(c, -2, "gemm: lower-only update needs a square C");
@@ -241,16 +238,20 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g) {
     // (in-place panel solves), otherwise 128x64 tiles with two CTAs per SM so one CTA's epilogue
     // overlaps the other's main loop.
     const bool wide = (g.N > 64 && g.N <= 128 && !g.lower);
+    const bool s3 = (c->opt_gemm_stages == 3);
     switch (form) {
         case GEMM_NT:
-            return wide ? launch<128, 128, 64, 32, true, true, 3, 1>(c, g)
-                        : launch<128, 64, 64, 32, true, true, 4, 2>(c, g);
+            if (wide) return launch<128, 128, 64, 32, true, true, 3, 1>(c, g, stream);
+            return s3 ? launch<128, 64, 64, 32, true, true, 3, 2>(c, g, stream)
+                      : launch<128, 64, 64, 32, true, true, 4, 2>(c, g, stream);
         case GEMM_NN:
-            return wide ? launch<128, 128, 64, 32, true, false, 3, 1>(c, g)
-                        : launch<128, 64, 64, 32, true, false, 4, 2>(c, g);
+            if (wide) return launch<128, 128, 64, 32, true, false, 3, 1>(c, g, stream);
+            return s3 ? launch<128, 64, 64, 32, true, false, 3, 2>(c, g, stream)
+                      : launch<128, 64, 64, 32, true, false, 4, 2>(c, g, stream);
         case GEMM_TN:
-            return wide ? launch<128, 128, 64, 32, false, false, 3, 1>(c, g)
-                        : launch<128, 64, 64, 32, false, false, 4, 2>(c, g);
+            if (wide) return launch<128, 128, 64, 32, false, false, 3, 1>(c, g, stream);
+            return s3 ? launch<128, 64, 64, 32, false, false, 3, 2>(c, g, stream)
+                      : launch<128, 64, 64, 32, false, false, 4, 2>(c, g, stream);
     }
     return fail(c, -2, "gemm: unknown form");
 }
