@@ -22,6 +22,7 @@ _PROTOS = {
     "gprb200_launch_count": (C.c_int64, [C.c_void_p]),
     "gprb200_phase_ms": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
+    "gprb200_get_stat": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_double)]),
     "gprb200_set_kernel": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]),
     "gprb200_set_kernel_params": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "gprb200_set_train": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_double]),
@@ -159,6 +160,11 @@ class Handle:
 
     def set_option(self, name, value):
         self._ck(self.lib.gprb200_set_option(self.h, name.encode(), int(value)))
+
+    def get_stat(self, name):
+        v = C.c_double()
+        self._ck(self.lib.gprb200_get_stat(self.h, name.encode(), C.byref(v)))
+        return v.value
 
     def synchronize(self):
         self._ck(self.lib.gprb200_synchronize(self.h))

@@ -395,11 +395,27 @@ int gprb200_phase_ms(gprb200_handle h, double* ms) {
     return 0;
 }
 
+int gprb200_get_stat(gprb200_handle h, const char* name, double* out) {
+    if (!h || !name || !out) return -2;
+    struct { const char* n; double v; } st[] = {
+        {"tb_ms", h->prof_tb_ms}, {"tb_flops", h->prof_tb_flops}, {"tb_launches", h->prof_tb_launches},
+        {"gemv_ms", h->prof_gemv_ms}, {"gemv_bytes", h->prof_gemv_bytes}, {"gemv_launches", h->prof_gemv_launches},
+        {"logdet", h->logdet}};
+    for (auto& e : st)
+        if (!strcmp(name, e.n)) {
+            *out = e.v;
+            return 0;
+        }
+    return fail(h, -2, std::string("get_stat: unknown statistic '") + name + "'");
+}
+
 int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
         {"gram_lower_only", &h->opt_gram_lower_only}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead},
-        {"gemm_stages", &h->opt_gemm_stages}, {"solve_left_min_m", &h->opt_solve_left_min_m}};
+        {"gemm_stages", &h->opt_gemm_stages}, {"solve_left_min_m", &h->opt_solve_left_min_m},
+        {"profile", &h->opt_profile}};
+    if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
     for (auto& o : opts)
         if (!strcmp(name, o.n)) {
             *o.p = value;

@@ -68,6 +68,9 @@ struct Ctx {
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
     int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
     cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel
+    int64_t opt_profile = 0;      // time every trailing-update GEMM launch with CUDA events (bench.py roofline)
+    double prof_tb_ms = 0.0, prof_tb_flops = 0.0, prof_tb_launches = 0.0;  // last factorisation
+    double prof_gemv_ms = 0.0, prof_gemv_bytes = 0.0, prof_gemv_launches = 0.0;  // accumulated since reset
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double phase_ms[GPRB200_T_COUNT] = {0};

@@ -11,6 +11,7 @@
 // INFO follows LAPACK dpotrf: k > 0 = leading minor of order k is not positive definite.
 #include "common.cuh"
 #include <math.h>
+#include <vector>
 
 namespace gprb200 {
 
@@ -161,6 +162,8 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
         GP_CUDA(c, cudaEventRecord(ev_ta, sm));  // panel 0 waits for everything queued so far (the Gram build)
     }
     int rc = 0;
+    std::vector<cudaEvent_t> pev;   // opt_profile: (start, stop) per trailing-update launch
+    std::vector<double> pflops;
     for (int64_t K0 = 0; K0 < N && rc == 0; K0 += NBO) {
         const int64_t W = (N - K0 < NBO) ? (N - K0) : NBO;
         if (la) GP_CUDA(c, cudaStreamWaitEvent(sp, ev_ta, 0));
@@ -188,12 +191,38 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
             GemmArgs tb{};
             tb.A = Pb; tb.lda = ld; tb.B = Pb; tb.ldb = ld; tb.C = A + (K0 + W + W2) * ld + (K0 + W + W2); tb.ldc = ld;
             tb.M = (int)mb; tb.N = (int)mb; tb.K = (int)W; tb.alpha = -1.0; tb.beta = 1.0; tb.lower = 1;
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (c->opt_profile) {
+                cudaEventCreate(&e0);
+                cudaEventCreate(&e1);
+                cudaEventRecord(e0, sm);
+            }
             rc = gemm(c, GEMM_NT, tb, sm);
+            if (c->opt_profile) {
+                cudaEventRecord(e1, sm);
+                pev.push_back(e0);
+                pev.push_back(e1);
+                pflops.push_back((double)mb * (double)(mb + 1) * (double)W);  // 2 * (mb (mb+1) / 2) * W: lower triangle only
+            }
         }
     }
     if (la) {
         cudaEventDestroy(ev_panel);
         cudaEventDestroy(ev_ta);
+    }
+    if (c->opt_profile) {
+        c->prof_tb_ms = c->prof_tb_flops = c->prof_tb_launches = 0.0;
+        for (size_t i = 0; i + 1 < pev.size(); i += 2) {
+            float ms = 0.f;
+            cudaEventSynchronize(pev[i + 1]);
+            if (cudaEventElapsedTime(&ms, pev[i], pev[i + 1]) == cudaSuccess) {
+                c->prof_tb_ms += ms;
+                c->prof_tb_flops += pflops[i / 2];
+                c->prof_tb_launches += 1.0;
+            }
+            cudaEventDestroy(pev[i]);
+            cudaEventDestroy(pev[i + 1]);
+        }
     }
     if (rc) return rc;
     if (info_host) {

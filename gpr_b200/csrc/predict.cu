@@ -88,10 +88,28 @@ int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, in
     } else {
         GP_CUDA(c, cudaMallocAsync(&partial, need, c->stream));
     }
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c->opt_profile) {
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0, c->stream);
+    }
     gemv_t_kernel<<<dim3((unsigned)col_blocks, (unsigned)splits), GV_THREADS, sizeof(double) * rows_per_split,
                     c->stream>>>(kx, A, lda, N, M, rows_per_split, partial, splits == 1 ? 0 : ldp);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
+    if (c->opt_profile) {
+        cudaEventRecord(e1, c->stream);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) {
+            c->prof_gemv_ms += ms;
+            c->prof_gemv_bytes += 8.0 * (double)N * (double)M;  // algorithmic: alpha is read once
+            c->prof_gemv_launches += 1.0;
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    }
     if (splits > 1) {
         gemv_reduce_kernel<<<(unsigned)((M + 255) / 256), 256, 0, c->stream>>>(partial, ldp, (int)splits, M, out);
         ++c->launches;

@@ -83,6 +83,10 @@ int64_t gprb200_launch_count(gprb200_handle h);
 int gprb200_phase_ms(gprb200_handle h, double* ms /* [GPRB200_T_COUNT] */);
 /* tuning knobs: "nb" (Cholesky block), "gram_lower_only" ... returns <0 for unknown names */
 int gprb200_set_option(gprb200_handle h, const char* name, int64_t value);
+/* with option "profile" = 1: per-launch CUDA-event statistics of the dominant kernels.
+ * "tb_ms"/"tb_flops"/"tb_launches": SYRK trailing-update GEMM launches of the last factorisation;
+ * "gemv_ms"/"gemv_bytes"/"gemv_launches": Predict GEMV launches since "profile" was last set. */
+int gprb200_get_stat(gprb200_handle h, const char* name, double* out);
 
 /* ---- model definition ------------------------------------------------------------------ */
 /* replaces Kernel<T> virtual dispatch per matrix element (lib/GaussianProcess.cpp:392) */
