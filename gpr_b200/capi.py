@@ -40,6 +40,7 @@ _PROTOS = {
     "gprb200_get_core": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_factor": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_logdet": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "gprb200_spd_inverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_double)]),
     "gprb200_predict": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "gprb200_predict_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_posterior_cov": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
@@ -212,6 +213,15 @@ class Handle:
         L = np.empty((self.N, self.N))
         self._ck(self.lib.gprb200_get_factor(self.h, _ptr(L)))
         return L
+
+    def spd_inverse(self, A):
+        """InvertKernelMatrix for an arbitrary SPD host matrix; returns (inverse, logdet)."""
+        A = _f64(A)
+        n = A.shape[0]
+        out = np.empty((n, n))
+        v = C.c_double()
+        self._ck(self.lib.gprb200_spd_inverse(self.h, _ptr(A), n, _ptr(out), C.byref(v)))
+        return out, v.value
 
     def logdet(self):
         v = C.c_double()

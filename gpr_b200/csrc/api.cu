@@ -599,6 +599,26 @@ int gprb200_get_logdet(gprb200_handle h, double* logdet) {
     return 0;
 }
 
+int gprb200_spd_inverse(gprb200_handle h, const double* A, int64_t n, double* Ainv, double* logdet) {
+    if (!h || !A || !Ainv || n <= 0) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    const int64_t ld = round_up(n, 16), nblk = (n + NB - 1) / NB;
+    TempBuf L(c), invL(c), C(c);
+    GP_TRY(L.alloc((size_t)n * ld));
+    GP_TRY(invL.alloc((size_t)nblk * NB * NB));
+    GP_TRY(C.alloc((size_t)n * ld));
+    GP_TRY(h2d_2d(c, L.p, ld, A, n, n));
+    int info = 0;
+    GP_TRY(potrf_blocked(c, L.p, ld, n, invL.p, &info));
+    if (info != 0)
+        return fail(c, info, "InvertKernelMatrix: matrix is not positive definite (leading minor of order " +
+                                 std::to_string(info) + ")");
+    if (logdet) GP_TRY(logdet_from_factor(c, L.p, ld, n, logdet));
+    GP_TRY(inverse_from_factor(c, L.p, ld, invL.p, n, C.p, ld));
+    return d2h_2d(c, Ainv, C.p, ld, n, n);
+}
+
 int gprb200_predict_dev(gprb200_handle h, const double* dXs, int64_t T, double* d_mean, int64_t ld_mean,
                         double* d_ci) {
     if (!h) return -2;

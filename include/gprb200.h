@@ -128,6 +128,11 @@ int gprb200_get_factor(gprb200_handle h, double* L /* N x N */);
 /* log det(K + sigma^2 I) = 2 sum log L_ii (replaces the long-double determinant, lib/GaussianProcess.cpp:527) */
 int gprb200_get_logdet(gprb200_handle h, double* logdet);
 
+/* InvertKernelMatrix (lib/GaussianProcess.cpp:531-618; include/LAPACKUtils.h:38-73) for an arbitrary symmetric
+ * positive-definite host matrix A (n x n): Ainv = inv(A) through the same Cholesky kernels, logdet (may be NULL)
+ * = log det A. Does not touch the model held by the handle. Returns k > 0 if the leading minor k is not SPD. */
+int gprb200_spd_inverse(gprb200_handle h, const double* A, int64_t n, double* Ainv, double* logdet);
+
 /* ---- Predict ----------------------------------------------------------------------------- */
 /* Predict (lib/GaussianProcess.cpp:55-61) for T test points at once; T = 1 is the app's call.
  * Xs: T x d.  mean: T x M.  ci (may be NULL): T values of GetCredibleInterval (:103-114),

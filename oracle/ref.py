@@ -1,6 +1,6 @@
 """ctypes access to oracle/_ref/libgpr_ref.so: the reference's OWN code (lib/GaussianProcess.cpp,
 include/Kernel.h, KernelFactory.h, Likelihood.h, LAPACKUtils.h compiled unmodified from /root/reference
-against oracle/eigen_shim and scipy's OpenBLAS; recipe: oracle/Makefile).
+against third_party/eigen_lite and scipy's OpenBLAS; recipe: oracle/Makefile).
 
 TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's CPU baseline legs.
 """

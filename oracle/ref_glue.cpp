@@ -4,7 +4,7 @@
 // lie under /root/reference (never copied into this repository):
 //     lib/GaussianProcess.cpp  (which pulls include/GaussianProcess.h, Kernel.h, KernelFactory.h,
 //                               Likelihood.h, LAPACKUtils.h, MatrixIO.h)
-// compiled against oracle/eigen_shim (Eigen / boost::filesystem stand-ins) and linked with the same
+// compiled against third_party/eigen_lite (Eigen / boost::filesystem stand-ins) and linked with the same
 // LAPACK routines the reference declares (include/LAPACKUtils.h:13-27), taken from scipy's OpenBLAS.
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference use the result.
 #include <cstring>

@@ -1,0 +1,34 @@
+"""GPU tests of the C++ host API: (1) tests/cxx/gp_device_test.cpp (ports of the reference's deterministic tests with
+the same constants and thresholds, plus the additive batch / float / determinant-mode API); (2) the drop-in check:
+the reference's OWN test programs compiled UNMODIFIED against gpr_b200/cxx/include + libgplib.so (oracle/Makefile
+target dropin_tests; the binaries are prebuilt where /root/reference exists and travel to the GPU box)."""
+import glob
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def _run(exe, timeout=600):
+    p = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, cwd="/tmp")
+    return p.returncode, p.stdout + p.stderr
+
+
+def test_cxx_device_program():
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "gp_device_test")
+    assert os.path.exists(exe), "tests/cxx/bin/gp_device_test missing: run __graft_entry__.build()"
+    rc, out = _run(exe)
+    assert rc == 0 and "[failed]" not in out, out[-4000:]
+
+
+DROPIN = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "dropin", "*")))
+
+
+@pytest.mark.skipif(not DROPIN, reason="oracle/_ref/dropin not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("exe", DROPIN, ids=[os.path.basename(e) for e in DROPIN])
+def test_reference_test_program_passes_against_this_library(exe):
+    rc, out = _run(exe, timeout=1200)
+    assert rc == 0 and "[failed]" not in out, out[-4000:]
