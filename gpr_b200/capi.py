@@ -41,6 +41,14 @@ _PROTOS = {
     "gprb200_get_factor": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_logdet": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "gprb200_spd_inverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_double)]),
+    "gprb200_gemm_dev": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_void_p, C.c_int64,
+                                   C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_int64, C.c_int]),
+    "gprb200_gram_block_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64]),
+    "gprb200_potrf_panel_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
+                                          C.POINTER(C.c_int)]),
+    "gprb200_trsm_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                   C.c_int64, C.c_int]),
+    "gprb200_logdet_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_double)]),
     "gprb200_predict": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "gprb200_predict_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_posterior_cov": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),

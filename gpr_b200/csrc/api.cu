@@ -413,7 +413,7 @@ int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
         {"gram_lower_only", &h->opt_gram_lower_only}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead},
-        {"gemm_stages", &h->opt_gemm_stages}, {"solve_left_min_m", &h->opt_solve_left_min_m},
+        {"gemm_stages", &h->opt_gemm_stages}, {"gemm_variant", &h->opt_gemm_variant}, {"solve_left_min_m", &h->opt_solve_left_min_m},
         {"profile", &h->opt_profile}};
     if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
     for (auto& o : opts)
@@ -617,6 +617,64 @@ int gprb200_spd_inverse(gprb200_handle h, const double* A, int64_t n, double* Ai
     if (logdet) GP_TRY(logdet_from_factor(c, L.p, ld, n, logdet));
     GP_TRY(inverse_from_factor(c, L.p, ld, invL.p, n, C.p, ld));
     return d2h_2d(c, Ainv, C.p, ld, n, n);
+}
+
+int gprb200_gemm_dev(gprb200_handle h, int form, int64_t M, int64_t N, int64_t K, double alpha, const double* dA,
+                     int64_t lda, const double* dB, int64_t ldb, double beta, double* dC, int64_t ldc, int lower) {
+    if (!h) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, form >= 0 && form <= 2 && M >= 0 && N >= 0 && K >= 0 && M < (1ll << 31) && N < (1ll << 31) &&
+                          K < (1ll << 31), "gemm_dev: bad form or extents"));
+    GemmArgs g{};
+    g.A = dA; g.lda = lda; g.B = dB; g.ldb = ldb; g.C = dC; g.ldc = ldc;
+    g.M = (int)M; g.N = (int)N; g.K = (int)K; g.alpha = alpha; g.beta = beta; g.lower = lower ? 1 : 0;
+    return gemm(c, (GemmForm)form, g);
+}
+
+int gprb200_gram_block_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_t col0, int64_t ncols, double* dOut,
+                           int64_t ldo) {
+    if (!h || !dOut) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, c->have_train && c->have_kernel, "gram_block: need samples and a kernel"));
+    GP_TRY(require(c, row0 >= 0 && col0 >= 0 && nrows > 0 && ncols > 0 && row0 + nrows <= c->N && col0 + ncols <= c->N,
+                   "gram_block: block outside the N x N kernel matrix"));
+    GP_TRY(gram_build(c, c->dX + row0 * c->d, nrows, c->dX + col0 * c->d, ncols, dOut, ldo, false, false, 0.0));
+    // sigma^2 on the global diagonal (AddNoiseToKernelMatrix, lib/GaussianProcess.cpp:375-381)
+    const int64_t lo = row0 > col0 ? row0 : col0;
+    const int64_t hi = (row0 + nrows < col0 + ncols) ? row0 + nrows : col0 + ncols;
+    if (hi > lo && c->sigma != 0.0)
+        GP_TRY(add_diag(c, dOut + (lo - row0) * ldo + (lo - col0), ldo, hi - lo, c->sigma * c->sigma));
+    return 0;
+}
+
+int gprb200_potrf_panel_dev(gprb200_handle h, double* dP, int64_t ld, int64_t rows, int64_t w, double* dInvL, int* info) {
+    if (!h || !dP || !dInvL) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, rows >= w && w > 0 && (ld & 1) == 0, "potrf_panel: need rows >= w > 0 and an even leading dimension"));
+    int inf = 0;
+    GP_TRY(potrf_panel(c, dP, ld, rows, w, dInvL, 0, &inf));
+    if (info) *info = inf;
+    if (inf != 0)
+        return fail(c, inf, "potrf_panel: block column is not positive definite (local leading minor of order " +
+                                std::to_string(inf) + ")");
+    return 0;
+}
+
+int gprb200_trsm_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, double* dB,
+                     int64_t ldb, int64_t M, int transposed) {
+    if (!h || !dL || !dInvL || !dB) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    return transposed ? trsm_lower_bwd(c, dL, ldl, dInvL, n, dB, ldb, M) : trsm_lower_fwd(c, dL, ldl, dInvL, n, dB, ldb, M);
+}
+
+int gprb200_logdet_dev(gprb200_handle h, const double* dL, int64_t ld, int64_t n, double* logdet) {
+    if (!h || !dL || !logdet) return -2;
+    GP_TRY(use_device(h));
+    return logdet_from_factor(h, dL, ld, n, logdet);
 }
 
 int gprb200_predict_dev(gprb200_handle h, const double* dXs, int64_t T, double* d_mean, int64_t ld_mean,

@@ -65,6 +65,7 @@ struct Ctx {
     int64_t opt_gram_lower_only = 1;
     int64_t opt_nbo = 1024;       // outer (trailing-update) block of the two-level Cholesky
     int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs
+    int64_t opt_gemm_variant = 0; // 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
     int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
     cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel
@@ -106,6 +107,7 @@ int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host /* P *
 int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream = nullptr);
 // potrf.cu
 int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host);
+int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* info_host);
 int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host);
 // solve.cu
 int trsm_lower_fwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,
@@ -116,6 +118,7 @@ int inverse_from_factor(Ctx* c, const double* L, int64_t ldl, const double* invL
 // util kernels (util.cu)
 int copy2d(Ctx* c, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t rows, int64_t cols);
 int fill2d(Ctx* c, double* dst, int64_t ldd, int64_t rows, int64_t cols, double v);
+int add_diag(Ctx* c, double* A, int64_t ld, int64_t n, double v);  // A(i,i) += v, i < n
 int set_identity(Ctx* c, double* dst, int64_t ldd, int64_t n);
 int symmetrize_from_lower(Ctx* c, double* A, int64_t ld, int64_t n);
 int zero_upper(Ctx* c, double* A, int64_t ld, int64_t n);

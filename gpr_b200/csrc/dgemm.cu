@@ -17,10 +17,11 @@
 //   NN: A is M x K (k contiguous), B is K x N (n contiguous)        C = A B     (forward solve, predict)
 //   TN: A is K x M (m contiguous), B is K x N (n contiguous)        C = A^T B   (backward solve)
 // Global->shared: 16-byte cp.async (LDGSTS) with zero-fill for ragged edges, STAGES-deep ring.
-// k-contiguous tiles are stored [row][16] with the 16-byte chunk index XOR-swizzled by (row & 7)
-// (the TMA SWIZZLE_128B pattern), so the 8x4 fragment read is 2 wavefronts = the 256-byte minimum.
-// m/n-contiguous tiles are stored [16][rows + 8]: rows t and t+1 of a fragment land in opposite
-// 16-bank halves.
+// A 64-bit LDS is served per HALF-warp (16 lanes x 8 B = one 128-byte wavefront if conflict-free); a half-warp
+// of the 8x4 DMMA fragment is 4 rows x 4 consecutive k = 4 x 32 B. k-contiguous tiles are stored [row][16] with
+// the 32-byte group index XOR-swizzled by (row & 3), m/n-contiguous tiles [16][rows + 4] (k-rows 32 B apart
+// mod 128), so those four 32-byte pieces always fall in four different bank groups: 2 wavefronts per LDS, the
+// minimum. (Round-1 ncu showed 4 per LDS with a (row & 7) 16-byte swizzle and the shared-memory pipe at 90 %.)
 #include "common.cuh"
 
 namespace gprb200 {
@@ -45,11 +46,11 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // tile geometry helpers ------------------------------------------------------------------------
 template <int ROWS, bool KC>
 struct OperandTile {
-    static constexpr int LD = KC ? BK : (ROWS + 8);
-    static constexpr int ELEMS = KC ? ROWS * BK : BK * (ROWS + 8);
+    static constexpr int LD = KC ? BK : (ROWS + 4);
+    static constexpr int ELEMS = KC ? ROWS * BK : BK * (ROWS + 4);
     // element (r = row in tile, k = 0..15)
     __device__ static __forceinline__ int idx(int r, int k) {
-        if (KC) return r * BK + ((((k >> 1) ^ (r & 7)) << 1) | (k & 1));
+        if (KC) return r * BK + ((((k >> 1) ^ ((r & 3) << 1)) << 1) | (k & 1));
         return k * LD + r;
     }
     // cooperative async load of one k-tile. base points at the operand's (row 0, k 0) element.
@@ -66,7 +67,7 @@ struct OperandTile {
                 int bytes = 0;
                 if (r < rows_valid) bytes = min(max((k_valid - k) * 8, 0), 16);
                 const double* src = bytes ? (base + (int64_t)r * ld + k) : base;
-                cp_async16(tile + r * BK + ((ch ^ (r & 7)) << 1), src, bytes);
+                cp_async16(tile + r * BK + ((ch ^ ((r & 3) << 1)) << 1), src, bytes);
             }
         } else {
             constexpr int CPR = ROWS / 2;  // chunks per k-row
@@ -84,26 +85,40 @@ struct OperandTile {
     }
 };
 
-// linear block index -> (ti, tj). lower: row-tile ti has tiles tj = 0 .. last(ti), where
-// last(ti) = min(tiles_n - 1, (ti*BM + BM - 1) / BN).
+// linear block index -> (ti, tj), rasterised for L2 reuse: CTAs are issued in groups of GM tile-rows, column-major
+// inside a group, so the ~300 co-resident CTAs share GM A-panels and a few dozen B-panels (a ~25 MB working set at
+// K = 1024) instead of one A-panel and ~300 B-panels (150 MB > L2), which made the SYRK update re-read its panel
+// 7x from DRAM in 128-byte pieces at a 256 KB stride (profiles/r01_ncu_summary.md).
+// lower: group g holds tile-rows [g GM, (g+1) GM) and R GM (g+1) tile-columns (R = BM / BN); tiles right of the
+// diagonal and rows past the edge exit at once.
+constexpr int GM = 8;
 template <int BM, int BN>
-__device__ __forceinline__ void map_tile(int lin, int lower, int tiles_n, int& ti, int& tj) {
+__device__ __forceinline__ bool map_tile(int lin, int lower, int tiles_m, int tiles_n, int& ti, int& tj) {
     if (!lower) {
-        ti = lin / tiles_n;
-        tj = lin - ti * tiles_n;
-        return;
+        const int width = GM * tiles_n;
+        const int group = lin / width;
+        const int first = group * GM;
+        const int gsize = min(tiles_m - first, GM);
+        const int local = lin - group * width;
+        ti = first + local % gsize;
+        tj = local / gsize;
+        return true;
     }
-    constexpr int R = BM / BN;  // BM is a multiple of BN; row-tile ti owns R*(ti+1) column tiles (before clamping)
-    // unclamped prefix: R * ti (ti + 1) / 2
-    int t = (int)((sqrt(1.0 + 8.0 * (double)lin / R) - 1.0) * 0.5);
-    while ((int64_t)R * (t + 1) * (t + 2) / 2 <= lin) ++t;
-    while ((int64_t)R * t * (t + 1) / 2 > lin) --t;
-    ti = t;
-    tj = lin - (int)((int64_t)R * t * (t + 1) / 2);
+    constexpr int R = BM / BN;
+    constexpr int64_t Q = (int64_t)GM * GM * R;  // tiles of group g: Q (g + 1); prefix(g) = Q g (g + 1) / 2
+    int gidx = (int)((sqrt(1.0 + 8.0 * (double)lin / (double)Q) - 1.0) * 0.5);
+    while (Q * (gidx + 1) * (gidx + 2) / 2 <= lin) ++gidx;
+    while (Q * gidx * (gidx + 1) / 2 > lin) --gidx;
+    const int local = lin - (int)(Q * gidx * (gidx + 1) / 2);
+    ti = gidx * GM + local % GM;
+    tj = local / GM;
+    return ti < tiles_m && tj < tiles_n && (int64_t)tj * BN <= (int64_t)ti * BM + BM - 1;
 }
 
-template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB>
-__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel(GemmArgs g, int tiles_n) {
+// STAGES k-tiles of BK live in the shared-memory ring; KSTEP of them are consumed per CTA barrier
+// (KSTEP = 2 halves the barrier rate at the same BK = 16 tile geometry).
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
+__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel(GemmArgs g, int tiles_m, int tiles_n) {
     constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
     constexpr int WARPS_N = BN / WN;
     constexpr int FM = WM / 8, FN = WN / 8;
@@ -114,9 +129,9 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     double* sB = smem + STAGES * TA::ELEMS;
 
     int ti, tj;
-    map_tile<BM, BN>(blockIdx.x, g.lower, tiles_n, ti, tj);
+    if (!map_tile<BM, BN>(blockIdx.x, g.lower, tiles_m, tiles_n, ti, tj)) return;
     const int m0 = ti * BM, n0 = tj * BN;
-    if (m0 >= g.M || n0 >= g.N) return;  // (cannot happen for the grids we launch; cheap guard)
+    if (m0 >= g.M || n0 >= g.N) return;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
@@ -142,31 +157,44 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
 #pragma unroll
         for (int j = 0; j < FN; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
+    static_assert(STAGES % KSTEP == 0 && STAGES / KSTEP >= 2, "ring must hold at least two barrier groups");
+    constexpr int GROUPS = STAGES / KSTEP;
+    const int ng = (nk + KSTEP - 1) / KSTEP;
+    auto issue_group = [&](int gi) {
 #pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) {
-        if (s < nk) issue(s);
+        for (int u = 0; u < KSTEP; ++u)
+            if (gi * KSTEP + u < nk) issue(gi * KSTEP + u);
+    };
+#pragma unroll
+    for (int s = 0; s < GROUPS - 1; ++s) {
+        if (s < ng) issue_group(s);
         cp_async_commit();
     }
 
-    for (int kt = 0; kt < nk; ++kt) {
-        cp_async_wait<STAGES - 2>();
+    for (int gi = 0; gi < ng; ++gi) {
+        cp_async_wait<GROUPS - 2>();
         __syncthreads();
-        if (kt + STAGES - 1 < nk) issue(kt + STAGES - 1);
+        if (gi + GROUPS - 1 < ng) issue_group(gi + GROUPS - 1);
         cp_async_commit();
 
-        const double* a_t = sA + (kt % STAGES) * TA::ELEMS;
-        const double* b_t = sB + (kt % STAGES) * TB::ELEMS;
 #pragma unroll
-        for (int kk = 0; kk < BK / 4; ++kk) {
-            double af[FM], bf[FN];
+        for (int u = 0; u < KSTEP; ++u) {
+            const int kt = gi * KSTEP + u;
+            if (KSTEP > 1 && kt >= nk) break;
+            const double* a_t = sA + (kt % STAGES) * TA::ELEMS;
+            const double* b_t = sB + (kt % STAGES) * TB::ELEMS;
 #pragma unroll
-            for (int i = 0; i < FM; ++i) af[i] = a_t[TA::idx(wm0 + i * 8 + grp, kk * 4 + t4)];
+            for (int kk = 0; kk < BK / 4; ++kk) {
+                double af[FM], bf[FN];
 #pragma unroll
-            for (int j = 0; j < FN; ++j) bf[j] = b_t[TB::idx(wn0 + j * 8 + grp, kk * 4 + t4)];
+                for (int i = 0; i < FM; ++i) af[i] = a_t[TA::idx(wm0 + i * 8 + grp, kk * 4 + t4)];
 #pragma unroll
-            for (int i = 0; i < FM; ++i)
+                for (int j = 0; j < FN; ++j) bf[j] = b_t[TB::idx(wn0 + j * 8 + grp, kk * 4 + t4)];
 #pragma unroll
-                for (int j = 0; j < FN; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+                for (int i = 0; i < FM; ++i)
+#pragma unroll
+                    for (int j = 0; j < FN; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+            }
         }
     }
     cp_async_wait<0>();
@@ -200,27 +228,25 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB>
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
 static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
     using TA = OperandTile<BM, AKC>;
     using TB = OperandTile<BN, BKC>;
     constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
     constexpr size_t SMEM = sizeof(double) * STAGES * (TA::ELEMS + TB::ELEMS);
-    auto kern = dgemm_kernel<BM, BN, WM, WN, AKC, BKC, STAGES, MINB>;
+    auto kern = dgemm_kernel<BM, BN, WM, WN, AKC, BKC, STAGES, MINB, KSTEP>;
     GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     const int64_t tm = (g.M + BM - 1) / BM, tn = (g.N + BN - 1) / BN;
     int64_t grid;
     if (g.lower) {
         constexpr int R = BM / BN;
-        grid = 0;
-        // row-tile ti owns min(tn, R*(ti+1)) tiles; the kernel's closed form assumes no clamping,
-        // which holds because the trailing matrix is square (M == N).
-        grid = (int64_t)R * tm * (tm + 1) / 2;
+        const int64_t ngroups = (tm + GM - 1) / GM;
+        grid = (int64_t)GM * GM * R * ngroups * (ngroups + 1) / 2;  // includes the early-exit tiles right of the diagonal
     } else {
         grid = tm * tn;
     }
     if (grid <= 0) return 0;
-    kern<<<(unsigned)grid, THREADS, SMEM, stream>>>(g, (int)tn);
+    kern<<<(unsigned)grid, THREADS, SMEM, stream>>>(g, (int)tm, (int)tn);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     return 0;
@@ -239,17 +265,38 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     // overlaps the other's main loop.
     const bool wide = (g.N > 64 && g.N <= 128 && !g.lower);
     const bool s3 = (c->opt_gemm_stages == 3);
+    const int variant = (int)c->opt_gemm_variant;
+    // variant 1: 64x16 warp tiles, 8 warps per CTA, 16 warps per SM (<= 128 registers): four warps per scheduler
+    // keep the DMMA pipe fed while another CTA sits in its epilogue or at a barrier.
     switch (form) {
         case GEMM_NT:
             if (wide) return launch<128, 128, 64, 32, true, true, 3, 1>(c, g, stream);
+            if (variant == 1) return launch<128, 64, 64, 16, true, true, 3, 2>(c, g, stream);
+            if (variant == 2) return launch<128, 64, 64, 32, true, true, 4, 2, 2>(c, g, stream);
+            if (variant == 3) return launch<128, 64, 64, 16, true, true, 4, 2, 2>(c, g, stream);
+            if (variant == 4) return launch<128, 128, 64, 32, true, true, 4, 1>(c, g, stream);
+            if (variant == 5) return launch<128, 128, 64, 16, true, true, 4, 1>(c, g, stream);
+            if (variant == 6) return launch<128, 128, 64, 16, true, true, 6, 1, 2>(c, g, stream);
             return s3 ? launch<128, 64, 64, 32, true, true, 3, 2>(c, g, stream)
                       : launch<128, 64, 64, 32, true, true, 4, 2>(c, g, stream);
         case GEMM_NN:
             if (wide) return launch<128, 128, 64, 32, true, false, 3, 1>(c, g, stream);
+            if (variant == 1) return launch<128, 64, 64, 16, true, false, 3, 2>(c, g, stream);
+            if (variant == 2) return launch<128, 64, 64, 32, true, false, 4, 2, 2>(c, g, stream);
+            if (variant == 3) return launch<128, 64, 64, 16, true, false, 4, 2, 2>(c, g, stream);
+            if (variant == 4) return launch<128, 128, 64, 32, true, false, 4, 1>(c, g, stream);
+            if (variant == 5) return launch<128, 128, 64, 16, true, false, 4, 1>(c, g, stream);
+            if (variant == 6) return launch<128, 128, 64, 16, true, false, 6, 1, 2>(c, g, stream);
             return s3 ? launch<128, 64, 64, 32, true, false, 3, 2>(c, g, stream)
                       : launch<128, 64, 64, 32, true, false, 4, 2>(c, g, stream);
         case GEMM_TN:
             if (wide) return launch<128, 128, 64, 32, false, false, 3, 1>(c, g, stream);
+            if (variant == 1) return launch<128, 64, 64, 16, false, false, 3, 2>(c, g, stream);
+            if (variant == 2) return launch<128, 64, 64, 32, false, false, 4, 2, 2>(c, g, stream);
+            if (variant == 3) return launch<128, 64, 64, 16, false, false, 4, 2, 2>(c, g, stream);
+            if (variant == 4) return launch<128, 128, 64, 32, false, false, 4, 1>(c, g, stream);
+            if (variant == 5) return launch<128, 128, 64, 16, false, false, 4, 1>(c, g, stream);
+            if (variant == 6) return launch<128, 128, 64, 16, false, false, 6, 1, 2>(c, g, stream);
             return s3 ? launch<128, 64, 64, 32, false, false, 3, 2>(c, g, stream)
                       : launch<128, 64, 64, 32, false, false, 4, 2>(c, g, stream);
     }

@@ -232,6 +232,22 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
     return 0;
 }
 
+// Tall panel (rows x w, leading dimension ld): Cholesky of the top w x w block and the rows below solved against
+// it, i.e. one block column of L. invL receives ceil(w / NB) inverted diagonal blocks. Used by the block-cyclic
+// multi-GPU factorisation, where the owner of a block column factors it before broadcasting it.
+int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* info_host) {
+    const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
+    GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
+    (void)col0;
+    GP_TRY(factor_panel(c, P, ld, rows, 0, w, invL, smem, c->stream));
+    if (info_host) {
+        GP_CUDA(c, cudaMemcpyAsync(info_host, c->dInfo, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        GP_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return 0;
+}
+
 int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host) {
     logdet_kernel<<<1, 1024, 0, c->stream>>>(L, ld, N, c->dScratch);
     ++c->launches;

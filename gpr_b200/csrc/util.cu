@@ -82,6 +82,18 @@ int fill2d(Ctx* c, double* dst, int64_t ldd, int64_t rows, int64_t cols, double 
     GP_CUDA(c, cudaGetLastError());
     return 0;
 }
+__global__ void add_diag_kernel(double* A, int64_t ld, int64_t n, double v) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) A[i * ld + i] += v;
+}
+int add_diag(Ctx* c, double* A, int64_t ld, int64_t n, double v) {
+    if (n <= 0) return 0;
+    add_diag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(A, ld, n, v);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    return 0;
+}
+
 int set_identity(Ctx* c, double* dst, int64_t ldd, int64_t n) {
     if (n <= 0) return 0;
     fill2d_kernel<<<grid_for(n * n, 256), 256, 0, c->stream>>>(dst, ldd, n, n, 0.0, 1);

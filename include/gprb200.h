@@ -133,6 +133,29 @@ int gprb200_get_logdet(gprb200_handle h, double* logdet);
  * = log det A. Does not touch the model held by the handle. Returns k > 0 if the leading minor k is not SPD. */
 int gprb200_spd_inverse(gprb200_handle h, const double* A, int64_t n, double* Ainv, double* logdet);
 
+/* ---- device-pointer building blocks (multi-GPU drivers, probes) -------------------------------------- */
+/* C = alpha op(A) op(B) + beta C on the FP64 tensor path, row-major, device pointers, 16-byte aligned, even lds.
+ * form 0 (NT): A is M x K, B is N x K, C = A B^T; 1 (NN): B is K x N; 2 (TN): A is K x M, B is K x N, C = A^T B.
+ * lower != 0 (square C): only tiles meeting the lower triangle are computed (SYRK-style trailing update).
+ * Replaces the Eigen / BLAS products of lib/GaussianProcess.cpp:60, :661. */
+int gprb200_gemm_dev(gprb200_handle h, int form, int64_t M, int64_t N, int64_t K, double alpha, const double* dA,
+                     int64_t lda, const double* dB, int64_t ldb, double beta, double* dC, int64_t ldc, int lower);
+
+/* Block [row0, row0+nrows) x [col0, col0+ncols) of K + sigma^2 I over the training samples (ComputeKernelMatrix +
+ * AddNoiseToKernelMatrix, lib/GaussianProcess.cpp:363-402, :375-381), written to a device buffer: lets every rank of
+ * a multi-GPU factorisation build exactly the block columns it owns, with no exchange. */
+int gprb200_gram_block_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_t col0, int64_t ncols, double* dOut,
+                           int64_t ldo);
+/* One block column of the Cholesky factor: dP is rows x w (ld), its top w x w block is factored in place and the
+ * rows below are solved against it (the dpotrf + dtrsm a blocked LAPACK dpotrf does per panel;
+ * include/LAPACKUtils.h:59-73). dInvL: ceil(w/128) blocks of 128 x 128 (inverted diagonal blocks, for trsm_dev). */
+int gprb200_potrf_panel_dev(gprb200_handle h, double* dP, int64_t ld, int64_t rows, int64_t w, double* dInvL, int* info);
+/* B <- L^-1 B (transposed = 0) or L^-T B (transposed != 0); L n x n lower (ldl), B n x M (ldb), dInvL as above. */
+int gprb200_trsm_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, double* dB,
+                     int64_t ldb, int64_t M, int transposed);
+/* 2 * sum_i log L(i,i) of an n x n device factor (replaces the determinant of lib/GaussianProcess.cpp:527) */
+int gprb200_logdet_dev(gprb200_handle h, const double* dL, int64_t ld, int64_t n, double* logdet);
+
 /* ---- Predict ----------------------------------------------------------------------------- */
 /* Predict (lib/GaussianProcess.cpp:55-61) for T test points at once; T = 1 is the app's call.
  * Xs: T x d.  mean: T x M.  ci (may be NULL): T values of GetCredibleInterval (:103-114),

@@ -1,0 +1,87 @@
+"""TEST INFRASTRUCTURE: a numpy stand-in for gpr_b200.dist.DeviceOps so that the multi-GPU host logic (ownership,
+schedule, look-ahead ordering, collectives) runs under gloo on CPU with world_size 2. Block operations are plain
+numpy/scipy on CPU tensors; the kernel matrix comes from the oracle. Never imported by the product."""
+import contextlib
+
+import numpy as np
+import scipy.linalg as sla
+import torch
+
+from oracle import gpr_oracle as orc
+
+
+class CpuOps:
+    device = torch.device("cpu")
+
+    def __init__(self, kernel_string, X, sigma):
+        self.k = orc.parse_kernel(kernel_string)
+        self.X = np.ascontiguousarray(X, dtype=np.float64)
+        self.sigma = float(sigma)
+        self.log = []  # (stream, op) trace, lets tests assert the schedule
+
+    def empty(self, rows, cols):
+        return torch.full((rows, cols), float("nan"), dtype=torch.float64)
+
+    def zeros(self, rows, cols):
+        return torch.zeros((rows, cols), dtype=torch.float64)
+
+    def from_host(self, a):
+        return torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64))
+
+    @contextlib.contextmanager
+    def on(self, which):
+        yield
+
+    def record(self, name, which):
+        self.log.append((which, "record", name))
+
+    def wait(self, name, which):
+        self.log.append((which, "wait", name))
+
+    def forget(self, name):
+        pass
+
+    def gram_block(self, row0, col0, out):
+        r, c = out.shape
+        K = orc.kernel_matrix(self.k, self.X[row0:row0 + r], self.X[col0:col0 + c])
+        for i in range(max(row0, col0), min(row0 + r, col0 + c)):
+            K[i - row0, i - col0] += self.sigma ** 2
+        out.copy_(torch.as_tensor(K))
+
+    def potrf_panel(self, P, invL, which="panel"):
+        self.log.append((which, "potrf", tuple(P.shape)))
+        w = P.shape[1]
+        A = P[:w].numpy()
+        try:
+            L = np.linalg.cholesky(np.tril(A) + np.tril(A, -1).T)
+        except np.linalg.LinAlgError:
+            return 1
+        P[:w] = torch.as_tensor(np.tril(L) + np.triu(A, 1))
+        if P.shape[0] > w:
+            P[w:] = torch.as_tensor(sla.solve_triangular(L, P[w:].numpy().T, lower=True).T)
+        return 0
+
+    def gemm(self, form, A, B, Cm, alpha, beta, which="main"):
+        self.log.append((which, "gemm" + form, tuple(Cm.shape)))
+        a, b = A.numpy(), B.numpy()
+        prod = a @ b.T if form == "NT" else (a @ b if form == "NN" else a.T @ b)
+        Cm.copy_(torch.as_tensor(alpha * prod + (beta * Cm.numpy() if beta != 0 else 0.0)))
+
+    def trsm(self, L, invL, B, transposed, which="main"):
+        Lm = np.tril(L.numpy())
+        B.copy_(torch.as_tensor(sla.solve_triangular(Lm, B.numpy(), lower=True, trans="T" if transposed else "N")))
+
+    def logdet(self, L):
+        return float(2.0 * np.sum(np.log(np.diag(L.numpy()))))
+
+    def inv_blocks(self, w):
+        return torch.zeros(1, 1, dtype=torch.float64)
+
+    def pad_cols(self, M):
+        return (M + 1) // 2 * 2
+
+    def synchronize(self):
+        pass
+
+    def close(self):
+        pass
