@@ -274,6 +274,10 @@ def run_gpu(args):
     predict = None if args.skip_predict else run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier,
                                                          max_over_ranks)
 
+    large = None
+    if world > 1 and not args.skip_large:
+        large = run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist)
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         cpu_baseline = run_cpu_baseline()
@@ -313,6 +317,8 @@ def run_gpu(args):
         }
         if predict:
             line["predict"] = predict
+        if large:
+            line["large_n"] = large
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
         if peaks:
@@ -421,6 +427,61 @@ def run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier, ma
 TRAFFIC_GEMV_BYTES_PER_LAUNCH = None
 
 
+def run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist):
+    """C5: ONE model of N = 131072 samples factored across all ranks (block-cyclic Cholesky, NCCL panel broadcasts,
+    gpr_b200/dist.py) + distributed solve. Strong scaling of a single large problem; device-timed, max over ranks."""
+    from gpr_b200 import dist as gd
+    N, nb = args.large_n, 1024
+    rng = np.random.default_rng(SEED + 131)
+    X = rng.uniform(-1, 1, (N, C3_D))
+    Y = (np.sin(3.0 * X[:, :1]) + 0.5 * np.cos(2.0 * X[:, 1:2] + X[:, 2:3]) + 0.1 * rng.standard_normal((N, 1)))
+    ops_, params = gpr_b200.KernelFactory.GetKernel(C3_KERNEL).lower()
+    ops = gd.DeviceOps(local_rank, ops_, params, X, C3_SIGMA)
+    # warm-up on a small problem with the same code path (NCCL communicator, allocator, kernel attributes)
+    warm = gd.BlockCyclicGP(ops, 8192, nb=nb)
+    warm.learn(Y[:8192])
+    del warm
+    torch.cuda.empty_cache()
+    gp = gd.BlockCyclicGP(ops, N, nb=nb)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    dist.barrier()
+    torch.cuda.synchronize()
+    with ops.on("main"):
+        ev[0].record()
+    gp.build_gram()
+    with ops.on("main"):
+        ev[1].record()
+    info = gp.factor()
+    with ops.on("main"):
+        ev[2].record()
+    alpha = gp.solve(Y) if info == 0 else None
+    with ops.on("main"):
+        ev[3].record()
+    torch.cuda.synchronize()
+    t = torch.tensor([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]),
+                      ev[0].elapsed_time(ev[3])], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    gram_ms, factor_ms, solve_ms, total_ms = (float(v) for v in t.tolist())
+    # residual on a sample of rows: ||(K + s^2 I) alpha - y|| over 512 rows, K rows regenerated by the Gram kernel
+    resid = None
+    if info == 0 and rank == 0:
+        rows = 512
+        Kr = ops.empty(rows, N)
+        with ops.on("main"):
+            ops.gram_block(N - rows, 0, Kr)
+            r = Kr @ alpha - ops.from_host(Y[N - rows:])
+            resid = float(torch.linalg.norm(r) / np.linalg.norm(Y[N - rows:]))
+    out = {"metric": "gp_learn_large_n_s", "N": N, "nb": nb, "n_gpus": world, "info": info,
+           "learn_s": total_ms * 1e-3, "gram_s": gram_ms * 1e-3, "cholesky_s": factor_ms * 1e-3, "solve_s": solve_ms * 1e-3,
+           "cholesky_tflops_total": N ** 3 / 3.0 / factor_ms * 1e-9,
+           "cholesky_frac_of_peak": N ** 3 / 3.0 / factor_ms * 1e-9 / (FP64_PEAK_TFLOPS * world),
+           "scaling": "strong (one N x N problem over all ranks)", "logdet": gp.logdet,
+           "bcast_GB_per_rank": gp.stats["bcast_bytes"] * 1e-9, "rel_residual_rows": resid,
+           "layout": "block-cyclic over a 1 x %d grid, lower triangle only, %.1f GB per GPU" % (world, 4.0 * N * N / world * 1e-9)}
+    ops.close()
+    return out
+
+
 def run_cpu_baseline():
     """The reference's own CPU code (oracle/_ref) on a bounded sample of the same workload, all host threads."""
     try:
@@ -452,6 +513,8 @@ def main():
     ap.add_argument("--predict-m", type=int, default=C2_M)
     ap.add_argument("--predict-steps", type=int, default=20)
     ap.add_argument("--skip-predict", action="store_true")
+    ap.add_argument("--skip-large", action="store_true")
+    ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")
     args = ap.parse_args()
