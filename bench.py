@@ -274,6 +274,10 @@ def run_gpu(args):
     predict = None if args.skip_predict else run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier,
                                                          max_over_ranks)
 
+    loglik = None
+    if rank == 0 and not args.skip_loglik:
+        loglik = run_loglik(torch, gpr_b200, local_rank)
+
     large = None
     if world > 1 and not args.skip_large:
         large = run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist)
@@ -319,6 +323,8 @@ def run_gpu(args):
             line["predict"] = predict
         if large:
             line["large_n"] = large
+        if loglik:
+            line["loglik"] = loglik
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
         if peaks:
@@ -427,6 +433,35 @@ def run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier, ma
 TRAFFIC_GEMV_BYTES_PER_LAUNCH = None
 
 
+def run_loglik(torch, gpr_b200, local_rank, N=16384, iters=3):
+    """C4: one iteration of the MaximumLikelihood loop (include/GaussianProcessInference.h:84-156): set parameters,
+    GaussianLogLikelihood value + gradient (include/Likelihood.h:231-285) at N = 16384, RationalQuadratic kernel.
+    Per iteration: Gram, Cholesky (N^3/3), explicit inverse from the factor (2N^3/3), fused trace contraction."""
+    rng = np.random.default_rng(SEED + 4)
+    X = rng.uniform(-1, 1, (N, C3_D))
+    Y = np.sin(3.0 * X[:, :1]) + 0.1 * rng.standard_normal((N, 1))
+    h = gpr_b200.Handle(local_rank)
+    ops, params = gpr_b200.KernelFactory.GetKernel("RationalQuadraticKernel(1,1.5,2,)").lower()
+    h.set_kernel(ops, params)
+    h.set_train(X, Y, 1.0)
+    h.loglik(1, True, True, False)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for it in range(iters):
+        h.set_kernel_params(np.asarray(params) * (1.0 + 0.01 * (it + 1)))   # P scalars cross the boundary per step
+        v, g, _ = h.loglik(1, True, True, False)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / iters * 1e3
+    ph = h.phase_ms()
+    h.close()
+    flops = N ** 3  # N^3/3 factor + 2N^3/3 inverse
+    return {"metric": "loglik_iteration_ms", "value": ms, "N": N, "kernel": "RationalQuadraticKernel", "P": 3,
+            "phase_ms": {k: ph[k] for k in ("gram", "potrf", "inverse", "solve", "loglik")},
+            "tflops_factor_plus_inverse": flops / ((ph["potrf"] + ph["inverse"]) * 1e-3) * 1e-12,
+            "reference_equivalent_flops": "2N^3 (LU inverse) + 2N^3/3 (long double det) + 3 x 2N^3 (trace GEMMs) = 3.8e13",
+            "last_value": float(v[0]), "last_grad": [float(x) for x in g]}
+
+
 def run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist):
     """C5: ONE model of N = 131072 samples factored across all ranks (block-cyclic Cholesky, NCCL panel broadcasts,
     gpr_b200/dist.py) + distributed solve. Strong scaling of a single large problem; device-timed, max over ranks."""
@@ -514,6 +549,7 @@ def main():
     ap.add_argument("--predict-steps", type=int, default=20)
     ap.add_argument("--skip-predict", action="store_true")
     ap.add_argument("--skip-large", action="store_true")
+    ap.add_argument("--skip-loglik", action="store_true")
     ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")

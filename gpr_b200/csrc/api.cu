@@ -119,15 +119,20 @@ int require(Ctx* c, bool cond, const char* msg) { return cond ? 0 : fail(c, -2, 
 int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, int64_t M, double sigma, bool on_device) {
     GP_TRY(require(c, N > 0 && d > 0 && X != nullptr, "set_train: need N > 0 samples of dimension d > 0"));
     GP_TRY(require(c, N < (1ll << 31) - 256 && M < (1ll << 31) - 256, "set_train: N and M must fit in 31 bits"));
-    free_model(c);
+    // Same shapes as the resident model (the hyper-parameter loop, repeated Learn calls): keep every device buffer.
+    // cudaFree / cudaMalloc of the 8.6 GB factor cost up to ~0.45 s per call at N = 32768 (tools/e2e_probe.py).
+    const bool reuse = c->have_train && c->N == N && c->d == d && c->M == (Y ? M : 0) && c->dX &&
+                       ((Y && M > 0) == (c->dY != nullptr));
+    if (!reuse) free_model(c);
+    c->have_factor = c->have_alpha = c->have_core = c->core_is_loaded = false;
     c->N = N; c->d = d; c->M = (Y ? M : 0); c->sigma = sigma;
     c->ldy = round_up(c->M > 0 ? c->M : 1, 16);
     c->ldk = round_up(N, 16);
-    GP_TRY(dev_alloc(c, &c->dX, (size_t)N * d));
+    if (!reuse) GP_TRY(dev_alloc(c, &c->dX, (size_t)N * d));
     const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     GP_CUDA(c, cudaMemcpyAsync(c->dX, X, sizeof(double) * N * d, kind, c->stream));
     if (Y && M > 0) {
-        GP_TRY(dev_alloc(c, &c->dY, (size_t)N * c->ldy));
+        if (!reuse) GP_TRY(dev_alloc(c, &c->dY, (size_t)N * c->ldy));
         if (c->ldy != M) GP_CUDA(c, cudaMemsetAsync(c->dY, 0, sizeof(double) * N * c->ldy, c->stream));
         GP_CUDA(c, cudaMemcpy2DAsync(c->dY, sizeof(double) * c->ldy, Y, sizeof(double) * M, sizeof(double) * M, N, kind,
                                      c->stream));
@@ -146,11 +151,13 @@ int ensure_factor(Ctx* c) {
     if (!c->dInvL) GP_TRY(dev_alloc(c, &c->dInvL, (size_t)nblk * NB * NB));
     {
         PhaseTimer t(c, GPRB200_T_GRAM);
+        GP_CUDA(c, cudaMemsetAsync(c->dInfo + 1, 0, sizeof(int), c->stream));
         GP_TRY(gram_build(c, c->dX, N, c->dX, N, c->dL, c->ldk, true, c->opt_gram_lower_only != 0,
-                          c->sigma * c->sigma));
+                          c->sigma * c->sigma, c->dInfo + 1));
         t.stop();
-        int bad = 0;
-        GP_TRY(check_finite(c, c->dL, N, N, c->ldk, true, &bad));
+        int bad = 0;  // the finite check (lib/GaussianProcess.cpp:399) is fused into the Gram kernel
+        GP_CUDA(c, cudaMemcpyAsync(&bad, c->dInfo + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        GP_CUDA(c, cudaStreamSynchronize(c->stream));
         t.resolve();
         if (bad)
             return fail(c, -3,
@@ -413,7 +420,7 @@ int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
         {"gram_lower_only", &h->opt_gram_lower_only}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead},
-        {"gemm_stages", &h->opt_gemm_stages}, {"gemm_variant", &h->opt_gemm_variant}, {"solve_left_min_m", &h->opt_solve_left_min_m},
+        {"gemm_stages", &h->opt_gemm_stages}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"solve_left_min_m", &h->opt_solve_left_min_m},
         {"profile", &h->opt_profile}};
     if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
     for (auto& o : opts)

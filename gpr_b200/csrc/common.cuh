@@ -65,7 +65,8 @@ struct Ctx {
     int64_t opt_gram_lower_only = 1;
     int64_t opt_nbo = 1024;       // outer (trailing-update) block of the two-level Cholesky
     int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs
-    int64_t opt_gemm_variant = 0; // 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
+    int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu
+    int64_t opt_gemm_variant = -1; // -1: auto; 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
     int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
     cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel
@@ -98,13 +99,14 @@ static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * 
 // kernels / drivers (each returns 0 or an error code; all async on c->stream) -----------------
 // gram.cu
 int gram_build(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, double* out, int64_t ldo,
-               bool symmetric, bool lower_only, double diag_add);
+               bool symmetric, bool lower_only, double diag_add, int* d_nonfinite = nullptr);
 int dgram_build(Ctx* c, double* out /* (P*N) x N */, int64_t ldo);
 int check_finite(Ctx* c, const double* A, int64_t rows, int64_t cols, int64_t ld, bool lower_only, int* bad_host);
 // fused likelihood-gradient contraction: out[p] = sum_ij S_ij * dK_p(i,j), S symmetric N x N (lds)
 int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host /* P */);
 // dgemm.cu
 int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream = nullptr);
+int gemm_skinny(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream);  // skinny.cu, n <= 8
 // potrf.cu
 int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host);
 int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* info_host);

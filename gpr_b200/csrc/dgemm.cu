@@ -257,6 +257,11 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     if (g.M <= 0 || g.N <= 0) return 0;
     if (!stream) stream = c->stream;
+    // few right-hand sides: HBM-bound streaming kernels instead of a mostly empty tensor-core tile (skinny.cu).
+    // In-place use (C aliasing B: the diagonal-block step Z_k = inv(L_kk) B_k) keeps the tile kernel, whose CTA
+    // reads all of its B columns before it writes.
+    if (!g.lower && g.N <= 8 && (form == GEMM_NN || form == GEMM_TN) && g.C != g.B && g.C != g.A && c->opt_skinny)
+        return gemm_skinny(c, form, g, stream);
     if (!aligned16(g.A) || !aligned16(g.B) || !aligned16(g.C) || (g.lda & 1) || (g.ldb & 1) || (g.ldc & 1))
         return fail(c, -2, "gemm: operands must be 16-byte aligned with even leading dimensions");
     if (g.lower && g.M != g.N) return fail(c, -2, "gemm: lower-only update needs a square C");
@@ -265,7 +270,8 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     // overlaps the other's main loop.
     const bool wide = (g.N > 64 && g.N <= 128 && !g.lower);
     const bool s3 = (c->opt_gemm_stages == 3);
-    const int variant = (int)c->opt_gemm_variant;
+    // auto (-1): the 16-warp variant wins where the epilogue is heavy (beta != 0 and a short K: the Cholesky updates)
+    const int variant = c->opt_gemm_variant >= 0 ? (int)c->opt_gemm_variant : ((g.beta != 0.0 && g.K <= 2048) ? 1 : 0);
     // variant 1: 64x16 warp tiles, 8 warps per CTA, 16 warps per SM (<= 128 registers): four warps per scheduler
     // keep the DMMA pipe fed while another CTA sits in its epilogue or at a barrier.
     switch (form) {

@@ -53,6 +53,11 @@ __device__ __forceinline__ void geo_init(Geo<DERIV>& g) {
 }
 
 template <bool DERIV>
+__device__ __forceinline__ void geo_acc_r2(Geo<DERIV>& g, double dx) {
+    g.r2 = fma(dx, dx, g.r2);
+}
+
+template <bool DERIV>
 __device__ __forceinline__ void geo_acc(Geo<DERIV>& g, const DevProg& P, double dx) {
     g.r2 = fma(dx, dx, g.r2);
 #pragma unroll

@@ -54,8 +54,253 @@ static int fwd_left(Ctx* c, const double* L, int64_t ldl, const double* invL, in
     return 0;
 }
 
+
+// ---- few right-hand sides (M <= 8): one fused streaming kernel per 128-row block step -----------------------------
+// The GEMM formulation above needs two dependent launches per block step and fills 1/64 of a tensor-core tile; with
+// M <= 8 the solve is bound by reading L once (4 N^2 bytes per sweep), so each step is ONE kernel:
+//   forward  step k: rows below block k get  b_r -= L[r, block k] . z_k  (one warp per row, a row segment of L is
+//            one contiguous 1 KB run); the CTA that owns the next 128 rows then applies inv(L_{k+1,k+1}) to them,
+//            so z_{k+1} is ready for the next launch.
+//   backward step k: columns left of block k get z_j -= sum_r L[block k row r, j] x_k[r] (one thread per column,
+//            coalesced across columns); the CTA holding block k-1's columns then applies inv(L_{k-1,k-1})^T.
+constexpr int TS_THREADS = 512;
+constexpr int TS_ROWS = NB;  // rows per CTA in the forward step
+constexpr size_t TS_SMEM = sizeof(double) * NB * NB;  // the owner CTA stages one inverted diagonal block
+
+__device__ __forceinline__ void ts_cp_async16(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem));
+}
+// whole 128 x 128 inverted block -> shared memory, asynchronously (issued before the CTA's streaming work so the
+// 128 KB fetch overlaps it); ts_wait_inv() before use.
+__device__ __forceinline__ void ts_prefetch_inv(double* sinv, const double* __restrict__ invk) {
+    for (int ch = threadIdx.x; ch < NB * NB / 2; ch += TS_THREADS) ts_cp_async16(sinv + ch * 2, invk + ch * 2);
+    asm volatile("cp.async.commit_group;\n" ::);
+}
+__device__ __forceinline__ void ts_wait_inv() {
+    asm volatile("cp.async.wait_group 0;\n" ::);
+    __syncthreads();
+}
+
+// z (n x NC) = inv(L_kk) b  or inv(L_kk)^T b, in place in B (row-major, ldb); sinv = the block in shared memory.
+template <int NC>
+__device__ __forceinline__ void apply_inv_block(const double* sinv, int n, double* B, int64_t ldb, int M, bool transposed,
+                                                double* sb /* [NB][NC] */, double* so /* [NB][NC] */) {
+    const int tid = threadIdx.x;
+    for (int e = tid; e < n * NC; e += TS_THREADS) {
+        const int r = e / NC, c = e - r * NC;
+        sb[e] = (c < M) ? B[(int64_t)r * ldb + c] : 0.0;
+    }
+    __syncthreads();
+    if (!transposed) {
+        // out[i] = sum_{j <= i} invL[i][j] b[j]: warp per row, lanes stride j (conflict-free), shuffle-reduce
+        const int warp = tid >> 5, lane = tid & 31;
+        for (int i = warp; i < n; i += TS_THREADS / 32) {
+            double acc[NC];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[c] = 0.0;
+            for (int j = lane; j <= i; j += 32) {
+                const double v = sinv[i * NB + j];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) acc[c] = fma(v, sb[j * NC + c], acc[c]);
+            }
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+            if (lane == 0) {
+#pragma unroll
+                for (int c = 0; c < NC; ++c) so[i * NC + c] = acc[c];
+            }
+        }
+    } else {
+        // out[i] = sum_{j >= i} invL[j][i] b[j]: thread per column i (conflict-free across i)
+        if (tid < n) {
+            double acc[NC];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[c] = 0.0;
+            for (int j = tid; j < n; ++j) {
+                const double v = sinv[j * NB + tid];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) acc[c] = fma(v, sb[j * NC + c], acc[c]);
+            }
+#pragma unroll
+            for (int c = 0; c < NC; ++c) so[tid * NC + c] = acc[c];
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < n * NC; e += TS_THREADS) {
+        const int r = e / NC, c = e - r * NC;
+        if (c < M) B[(int64_t)r * ldb + c] = so[e];
+    }
+}
+
+// k0 < 0: prologue (only z_0 = inv(L_00) b_0).
+template <int NC>
+__global__ void __launch_bounds__(TS_THREADS) trsv_fwd_step_kernel(const double* __restrict__ L, int64_t ldl,
+                                                                    const double* __restrict__ invL, int64_t N,
+                                                                    double* B, int64_t ldb, int M, int64_t k0) {
+    extern __shared__ __align__(16) double sinv[];
+    __shared__ double sz[NB * NC];
+    __shared__ double so[NB * NC];
+    const int tid = threadIdx.x;
+    if (k0 < 0) {
+        ts_prefetch_inv(sinv, invL);
+        ts_wait_inv();
+        apply_inv_block<NC>(sinv, (int)min((int64_t)NB, N), B, ldb, M, false, sz, so);
+        return;
+    }
+    const int n = NB;  // block k is full whenever rows remain below it
+    const int64_t k1 = k0 + n;
+    if (blockIdx.x == 0) ts_prefetch_inv(sinv, invL + (k1 / NB) * (int64_t)NB * NB);
+    for (int e = tid; e < n * NC; e += TS_THREADS) {
+        const int r = e / NC, c = e - r * NC;
+        sz[e] = (c < M) ? B[(k0 + r) * ldb + c] : 0.0;
+    }
+    __syncthreads();
+    const int64_t r_begin = k1 + (int64_t)blockIdx.x * TS_ROWS;
+    const int64_t r_end = min(N, r_begin + TS_ROWS);
+    const int warp = tid >> 5, lane = tid & 31;
+    constexpr int WARPS = TS_THREADS / 32;
+    // two rows per warp iteration: 4 independent 16-byte loads in flight per lane
+    for (int64_t r = r_begin + warp; r < r_end; r += 2 * WARPS) {
+        const int64_t r2 = r + WARPS;
+        const bool two = r2 < r_end;
+        const double* la = L + r * ldl + k0;
+        const double* lb = L + (two ? r2 : r) * ldl + k0;
+        double2 va[NB / 64], vb[NB / 64];
+#pragma unroll
+        for (int q = 0; q < NB / 64; ++q) {
+            va[q] = *reinterpret_cast<const double2*>(la + q * 64 + lane * 2);
+            vb[q] = *reinterpret_cast<const double2*>(lb + q * 64 + lane * 2);
+        }
+        double acca[NC], accb[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) acca[c] = accb[c] = 0.0;
+#pragma unroll
+        for (int q = 0; q < NB / 64; ++q) {
+            const int j = q * 64 + lane * 2;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                acca[c] = fma(va[q].y, sz[(j + 1) * NC + c], fma(va[q].x, sz[j * NC + c], acca[c]));
+                accb[c] = fma(vb[q].y, sz[(j + 1) * NC + c], fma(vb[q].x, sz[j * NC + c], accb[c]));
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                acca[c] += __shfl_xor_sync(0xffffffffu, acca[c], o);
+                accb[c] += __shfl_xor_sync(0xffffffffu, accb[c], o);
+            }
+        if (lane == 0) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c)
+                if (c < M) {
+                    B[r * ldb + c] -= acca[c];
+                    if (two) B[r2 * ldb + c] -= accb[c];
+                }
+        }
+    }
+    if (blockIdx.x == 0) {  // this CTA owns the next diagonal block's rows: finish z_{k+1}
+        ts_wait_inv();
+        const int n1 = (int)min((int64_t)NB, N - k1);
+        apply_inv_block<NC>(sinv, n1, B + k1 * ldb, ldb, M, false, sz, so);
+    }
+}
+
+// k0 = first row of block k, n = its height. prologue: only x_last = inv(L)^T z_last.
+template <int NC>
+__global__ void __launch_bounds__(TS_THREADS) trsv_bwd_step_kernel(const double* __restrict__ L, int64_t ldl,
+                                                                    const double* __restrict__ invL, double* B,
+                                                                    int64_t ldb, int M, int64_t k0, int n, int prologue) {
+    extern __shared__ __align__(16) double sinv[];
+    __shared__ double sx[NB * NC];
+    __shared__ double so[NB * NC];
+    const int tid = threadIdx.x;
+    if (prologue) {
+        ts_prefetch_inv(sinv, invL + (k0 / NB) * (int64_t)NB * NB);
+        ts_wait_inv();
+        apply_inv_block<NC>(sinv, n, B + k0 * ldb, ldb, M, true, sx, so);
+        return;
+    }
+    // the CTA whose columns include block k-1 (columns [k0 - NB, k0), inside one TS_THREADS-aligned chunk) also
+    // finishes x_{k-1}
+    const int64_t kprev = k0 - NB;
+    const bool owner = (int64_t)blockIdx.x == kprev / TS_THREADS;
+    if (owner) ts_prefetch_inv(sinv, invL + (kprev / NB) * (int64_t)NB * NB);
+    for (int e = tid; e < n * NC; e += TS_THREADS) {
+        const int r = e / NC, c = e - r * NC;
+        sx[e] = (c < M) ? B[(k0 + r) * ldb + c] : 0.0;
+    }
+    __syncthreads();
+    const int64_t j = (int64_t)blockIdx.x * TS_THREADS + tid;
+    if (j < k0) {
+        const double* lcol = L + k0 * ldl + j;
+        double acc[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) acc[c] = 0.0;
+#pragma unroll 16
+        for (int r = 0; r < n; ++r) {
+            const double v = lcol[(int64_t)r * ldl];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[c] = fma(v, sx[r * NC + c], acc[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+            if (c < M) B[j * ldb + c] -= acc[c];
+    }
+    if (owner) {
+        ts_wait_inv();
+        apply_inv_block<NC>(sinv, NB, B + kprev * ldb, ldb, M, true, sx, so);
+    }
+}
+
+template <int NC>
+static int trsv_fwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb, int M) {
+    GP_CUDA(c, cudaFuncSetAttribute(trsv_fwd_step_kernel<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TS_SMEM));
+    trsv_fwd_step_kernel<NC><<<1, TS_THREADS, TS_SMEM, c->stream>>>(L, ldl, invL, N, B, ldb, M, -1);
+    ++c->launches;
+    for (int64_t k0 = 0; k0 + NB < N; k0 += NB) {
+        const int64_t rows = N - k0 - NB;
+        trsv_fwd_step_kernel<NC><<<(unsigned)((rows + TS_ROWS - 1) / TS_ROWS), TS_THREADS, TS_SMEM, c->stream>>>(
+            L, ldl, invL, N, B, ldb, M, k0);
+        ++c->launches;
+    }
+    GP_CUDA(c, cudaGetLastError());
+    return 0;
+}
+
+template <int NC>
+static int trsv_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb, int M) {
+    const int64_t nblk = (N + NB - 1) / NB;
+    const int64_t klast = (nblk - 1) * NB;
+    GP_CUDA(c, cudaFuncSetAttribute(trsv_bwd_step_kernel<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TS_SMEM));
+    trsv_bwd_step_kernel<NC><<<1, TS_THREADS, TS_SMEM, c->stream>>>(L, ldl, invL, B, ldb, M, klast, (int)(N - klast), 1);
+    ++c->launches;
+    for (int64_t k0 = klast; k0 > 0; k0 -= NB) {
+        const int n = (int)((N - k0 < NB) ? (N - k0) : NB);
+        trsv_bwd_step_kernel<NC><<<(unsigned)((k0 + TS_THREADS - 1) / TS_THREADS), TS_THREADS, TS_SMEM, c->stream>>>(
+            L, ldl, invL, B, ldb, M, k0, n, 0);
+        ++c->launches;
+    }
+    GP_CUDA(c, cudaGetLastError());
+    return 0;
+}
+
+static int trsv_dispatch(Ctx* c, bool bwd, const double* L, int64_t ldl, const double* invL, int64_t N, double* B,
+                         int64_t ldb, int64_t M) {
+#define GP_TRSV(NC) (bwd ? trsv_bwd<NC>(c, L, ldl, invL, N, B, ldb, (int)M) : trsv_fwd<NC>(c, L, ldl, invL, N, B, ldb, (int)M))
+    if (M <= 1) return GP_TRSV(1);
+    if (M <= 2) return GP_TRSV(2);
+    if (M <= 4) return GP_TRSV(4);
+    return GP_TRSV(8);
+#undef GP_TRSV
+}
+
 int trsm_lower_fwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,
                    int64_t M) {
+    if (M <= 8 && c->opt_skinny && (ldl & 1) == 0) return trsv_dispatch(c, false, L, ldl, invL, N, B, ldb, M);
     return (M >= c->opt_solve_left_min_m) ? fwd_left(c, L, ldl, invL, N, B, ldb, M)
                                           : fwd_right(c, L, ldl, invL, N, B, ldb, M);
 }
@@ -106,16 +351,53 @@ static int bwd_left(Ctx* c, const double* L, int64_t ldl, const double* invL, in
 
 int trsm_lower_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,
                    int64_t M) {
+    if (M <= 8 && c->opt_skinny && (ldl & 1) == 0) return trsv_dispatch(c, true, L, ldl, invL, N, B, ldb, M);
     return (M >= c->opt_solve_left_min_m) ? bwd_left(c, L, ldl, invL, N, B, ldb, M)
                                           : bwd_right(c, L, ldl, invL, N, B, ldb, M);
 }
 
+// K5: C = (L L^T)^-1 from the factor, 2 N^3 / 3 flop (LAPACK dpotri's count; the reference calls dgetri / dpotri,
+// include/LAPACKUtils.h:50, :65). Two structured sweeps over C = I:
+//   forward  W = L^-1 is lower triangular: at block row k only columns [0, k0 + n) can be non-zero, so both GEMMs
+//            of the step are restricted to them (N^3 / 3 flop instead of N^3);
+//   backward C = L^-T W is symmetric: only its lower triangle is formed (row block i needs columns <= i), the
+//            update of the rows above block k is a lower-tiles-only GEMM (N^3 / 3 flop), then mirrored.
 int inverse_from_factor(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* C, int64_t ldc) {
     GP_TRY(set_identity(c, C, ldc, N));
-    GP_TRY(trsm_lower_fwd(c, L, ldl, invL, N, C, ldc, N));
-    GP_TRY(trsm_lower_bwd(c, L, ldl, invL, N, C, ldc, N));
-    // the two sweeps give a numerically (not bitwise) symmetric result; the reference's LU inverse is
-    // not exactly symmetric either. Mirror the lower triangle so C == C^T holds exactly.
+    for (int64_t k0 = 0; k0 < N; k0 += NB) {
+        const int n = (int)((N - k0 < NB) ? (N - k0) : NB);
+        const int64_t cols = k0 + n;
+        const double* invk = invL + (k0 / NB) * (int64_t)NB * NB;
+        double* Bk = C + k0 * ldc;
+        GemmArgs d{};
+        d.A = invk; d.lda = NB; d.B = Bk; d.ldb = ldc; d.C = Bk; d.ldc = ldc;
+        d.M = n; d.N = (int)cols; d.K = n; d.alpha = 1.0; d.beta = 0.0;
+        GP_TRY(gemm(c, GEMM_NN, d));
+        const int64_t m = N - k0 - n;
+        if (m <= 0) break;
+        GemmArgs u{};
+        u.A = L + (k0 + n) * ldl + k0; u.lda = ldl; u.B = Bk; u.ldb = ldc; u.C = C + (k0 + n) * ldc; u.ldc = ldc;
+        u.M = (int)m; u.N = (int)cols; u.K = n; u.alpha = -1.0; u.beta = 1.0;
+        GP_TRY(gemm(c, GEMM_NN, u));
+    }
+    const int64_t nblk = (N + NB - 1) / NB;
+    for (int64_t kb = nblk - 1; kb >= 0; --kb) {
+        const int64_t k0 = kb * NB;
+        const int n = (int)((N - k0 < NB) ? (N - k0) : NB);
+        const int64_t cols = k0 + n;
+        const double* invk = invL + kb * (int64_t)NB * NB;
+        double* Bk = C + k0 * ldc;
+        GemmArgs d{};
+        d.A = invk; d.lda = NB; d.B = Bk; d.ldb = ldc; d.C = Bk; d.ldc = ldc;
+        d.M = n; d.N = (int)cols; d.K = n; d.alpha = 1.0; d.beta = 0.0;
+        GP_TRY(gemm(c, GEMM_TN, d));
+        if (k0 == 0) break;
+        GemmArgs u{};  // rows [0, k0), columns [0, k0), lower tiles only
+        u.A = L + k0 * ldl; u.lda = ldl; u.B = Bk; u.ldb = ldc; u.C = C; u.ldc = ldc;
+        u.M = (int)k0; u.N = (int)k0; u.K = n; u.alpha = -1.0; u.beta = 1.0; u.lower = 1;
+        GP_TRY(gemm(c, GEMM_TN, u));
+    }
+    // the lower triangle is the result; mirror it so C == C^T holds exactly
     GP_TRY(symmetrize_from_lower(c, C, ldc, N));
     return 0;
 }

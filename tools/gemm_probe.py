@@ -32,6 +32,7 @@ def main():
               ("square 8192^3 NT", 0, 8192, 8192, 8192, 0.0, 0), ("square 8192^3 TN", 2, 8192, 8192, 8192, 0.0, 0)]
     import os
     variants = [int(v) for v in os.environ.get('VARIANTS', '0,1').split(',')]
+    h.set_option('gemm_stages', int(os.environ.get('STAGES', '3')))
     for variant in variants:
         h.set_option("gemm_variant", variant)
         for name, form, M, N, K, beta, lower in shapes:
