@@ -65,6 +65,7 @@ struct Ctx {
     int64_t opt_gram_lower_only = 1;
     int64_t opt_nbo = 1024;       // outer (trailing-update) block of the two-level Cholesky
     int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs
+    int64_t opt_potrf_tile = 2;    // 2: blocked register/shuffle diagonal-tile kernel, 1: unblocked shared-memory kernel
     int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu
     int64_t opt_gemm_variant = -1; // -1: auto; 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM

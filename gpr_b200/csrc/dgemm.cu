@@ -85,6 +85,48 @@ struct OperandTile {
     }
 };
 
+__device__ __forceinline__ void cp_async16_full(unsigned smem_addr, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_addr), "l"(gmem));
+}
+
+// Branch-free loader for interior tiles (all rows valid, k-tile fully inside K): each thread's chunks lie on an
+// arithmetic progression in global memory (stride gstride doubles) and in shared memory (stride sstride bytes),
+// so a k-tile is NI back-to-back LDGSTS with no predicates. The zero-filling OperandTile::load above handles edges.
+// (Round-1 SASS: the predicated path compiled to one branch diamond per 16-byte chunk, 12 per thread and k-tile,
+// fencing the DMMA stream at every k-tile.)
+template <int ROWS, bool KC, int THREADS>
+struct FastLoader {
+    static constexpr int CPR = KC ? (BK / 2) : (ROWS / 2);          // 16-byte chunks per tile row (KC) / per k-row
+    static constexpr int LINES = KC ? ROWS : BK;                      // rows (KC) or k-rows walked by the progression
+    static constexpr int STEP = THREADS / CPR;                        // lines advanced per chunk index i
+    static constexpr int NI = LINES / STEP;
+    static_assert(THREADS % CPR == 0 && LINES % STEP == 0, "tile does not split evenly over the CTA");
+    const double* src;   // chunk 0 of k-tile 0
+    int64_t gstride;     // doubles between consecutive chunks of this thread
+    unsigned dst;        // shared address of chunk 0 in stage 0
+    __device__ __forceinline__ void init(const double* base, int64_t ld, double* tile0, int tid) {
+        using T = OperandTile<ROWS, KC>;
+        const int line = tid / CPR, ch = tid - line * CPR;
+        if (KC) {
+            src = base + (int64_t)line * ld + ch * 2;
+            dst = (unsigned)__cvta_generic_to_shared(tile0 + line * BK + ((ch ^ ((line & 3) << 1)) << 1));
+            static_assert(!KC || (STEP % 4 == 0), "swizzle phase must be constant along the progression");
+        } else {
+            src = base + (int64_t)line * ld + ch * 2;
+            dst = (unsigned)__cvta_generic_to_shared(tile0 + line * T::LD + ch * 2);
+        }
+        gstride = (int64_t)STEP * ld;
+    }
+    // kofs: element offset of this k-tile from k-tile 0 (k0 for KC, k0 * ld otherwise); stage_bytes: ring offset
+    __device__ __forceinline__ void issue(int64_t kofs, unsigned stage_bytes) const {
+        using T = OperandTile<ROWS, KC>;
+        constexpr unsigned SSTRIDE = (KC ? STEP * BK : STEP * T::LD) * sizeof(double);
+        const double* p = src + kofs;
+#pragma unroll
+        for (int i = 0; i < NI; ++i) cp_async16_full(dst + stage_bytes + i * SSTRIDE, p + i * gstride);
+    }
+};
+
 // linear block index -> (ti, tj), rasterised for L2 reuse: CTAs are issued in groups of GM tile-rows, column-major
 // inside a group, so the ~300 co-resident CTAs share GM A-panels and a few dozen B-panels (a ~25 MB working set at
 // K = 1024) instead of one A-panel and ~300 B-panels (150 MB > L2), which made the SYRK update re-read its panel
@@ -142,9 +184,20 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     const int mrem = g.M - m0, nrem = g.N - n0;
     const int nk = (g.K + BK - 1) / BK;
 
+    FastLoader<BM, AKC, THREADS> fa;
+    FastLoader<BN, BKC, THREADS> fb;
+    fa.init(Abase, g.lda, sA, tid);
+    fb.init(Bbase, g.ldb, sB, tid);
+    const bool interior = (mrem >= BM) && (nrem >= BN);  // uniform across the CTA
+
     auto issue = [&](int kt) {
         const int buf = kt % STAGES;
         const int k0 = kt * BK;
+        if (interior && k0 + BK <= g.K) {
+            fa.issue(AKC ? (int64_t)k0 : (int64_t)k0 * g.lda, (unsigned)(buf * TA::ELEMS * sizeof(double)));
+            fb.issue(BKC ? (int64_t)k0 : (int64_t)k0 * g.ldb, (unsigned)(buf * TB::ELEMS * sizeof(double)));
+            return;
+        }
         const double* a = AKC ? (Abase + k0) : (Abase + (int64_t)k0 * g.lda);
         const double* b = BKC ? (Bbase + k0) : (Bbase + (int64_t)k0 * g.ldb);
         TA::template load<THREADS>(sA + buf * TA::ELEMS, a, g.lda, mrem, g.K - k0, tid);

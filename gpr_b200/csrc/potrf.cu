@@ -97,6 +97,189 @@ potrf_tile_kernel(double* __restrict__ A, int64_t lda, int n, double* __restrict
     }
 }
 
+// ---- potrf_tile2_kernel: 128 x 128 diagonal block, blocked (32-wide) inside one CTA ---------------------------------
+// Round-1 measurement: the unblocked kernel above needs ~512 CTA-wide barriers (~150 us per tile, 256 tiles per
+// N = 32768 factorisation = the whole serial panel time). Here each 32-column step is
+//   (1) diagonal 32 x 32 block factored AND inverted by one warp entirely in registers (shuffles, no barriers),
+//   (2) rows below: X = A inv(L_dd)^T as a small product over all warps,
+//   (3) trailing lower triangle: A -= X X^T,
+// three barriers per step; inv(L) of the whole tile is then assembled block-wise from the inverted diagonal blocks
+// (W_ij = -W_ii sum_k L_ik W_kj), two barriers per block distance.
+constexpr int P2_THREADS = 256;
+constexpr int P2_IB = 32;
+constexpr int P2_LD = NB + 1;
+constexpr size_t P2_SMEM = sizeof(double) * ((size_t)NB * P2_LD + 4 * P2_IB * (P2_IB + 1) + 3 * P2_IB * (P2_IB + 1) + NB);
+
+__global__ void __launch_bounds__(P2_THREADS, 1)
+potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restrict__ invL, int* info, int col0) {
+    extern __shared__ double sm2[];
+    double* S = sm2;                                   // [NB][P2_LD]: lower = A then L; strict upper = inv(L)^T blocks
+    double* Wd = S + NB * P2_LD;                       // [4][32][33]: inverses of the 32 x 32 diagonal blocks
+    double* Tm = Wd + 4 * P2_IB * (P2_IB + 1);         // [3][32][33]: products in flight
+    double* dW = Tm + 3 * P2_IB * (P2_IB + 1);         // [NB]: diagonal of inv(L)
+    __shared__ int bad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int WARPS = P2_THREADS / 32;
+    constexpr unsigned FULL = 0xffffffffu;
+    if (tid == 0) bad = 0;
+    // rows / columns >= n are padded with the identity so that every block is a full 32 x 32 problem
+    for (int e = tid; e < NB * NB; e += P2_THREADS) {
+        const int r = e / NB, c = e - r * NB;
+        double v = 0.0;
+        if (r < n && c <= r) v = A[(int64_t)r * lda + c];
+        else if (r >= n && c == r) v = 1.0;
+        S[r * P2_LD + c] = v;
+    }
+    __syncthreads();
+
+    for (int b = 0; b < NB / P2_IB; ++b) {
+        const int c0 = b * P2_IB;
+        if (c0 >= n) break;
+        // ---- (1) warp 0: Cholesky of the diagonal block, lane i owns row i; then its inverse, lane j owns column j
+        if (warp == 0) {
+            double a[P2_IB];
+#pragma unroll
+            for (int k = 0; k < P2_IB; ++k) a[k] = (k <= lane) ? S[(c0 + lane) * P2_LD + c0 + k] : 0.0;
+            int fail_at = -1;
+            double rdiag = 1.0;  // lane j keeps 1 / l_jj: the dependent chain has one rsqrt and no division per column
+#pragma unroll
+            for (int j = 0; j < P2_IB; ++j) {
+                const double djj = __shfl_sync(FULL, a[j], j);
+                if (fail_at < 0 && (!(djj > 0.0) || !isfinite(djj))) fail_at = j;  // uniform across the warp
+                const double rj = rsqrt(djj);
+                if (lane == j) {
+                    a[j] = djj * rj;  // l_jj = sqrt(d) = d * rsqrt(d)
+                    rdiag = rj;
+                } else if (lane > j) {
+                    a[j] = a[j] * rj;
+                }
+#pragma unroll
+                for (int k = j + 1; k < P2_IB; ++k) {
+                    const double lkj = __shfl_sync(FULL, a[j], k);
+                    if (lane >= k) a[k] = fma(-a[j], lkj, a[k]);
+                }
+            }
+            if (fail_at >= 0) {
+                if (lane == 0) {
+                    bad = 1;
+                    atomicCAS(info, 0, col0 + c0 + fail_at + 1);
+                }
+            } else {
+                // inverse: column j of W = inv(L_dd): w[j] = 1 / l_jj, w[i] = -(sum_{k=j}^{i-1} l_ik w[k]) / l_ii
+                double w[P2_IB];
+#pragma unroll
+                for (int i = 0; i < P2_IB; ++i) {
+                    double acc0 = 0.0, acc1 = 0.0;  // two chains halve the dependent FMA latency
+#pragma unroll
+                    for (int k = 0; k < i; ++k) {
+                        const double lik = __shfl_sync(FULL, a[k], i);
+                        if (k >= lane) {
+                            if (k & 1) acc1 = fma(lik, w[k], acc1);
+                            else acc0 = fma(lik, w[k], acc0);
+                        }
+                    }
+                    const double ri = __shfl_sync(FULL, rdiag, i);
+                    w[i] = (i == lane) ? ri : ((i > lane) ? -(acc0 + acc1) * ri : 0.0);
+                }
+#pragma unroll
+                for (int k = 0; k < P2_IB; ++k)
+                    if (k <= lane) S[(c0 + lane) * P2_LD + c0 + k] = a[k];
+#pragma unroll
+                for (int i = 0; i < P2_IB; ++i) Wd[(b * P2_IB + i) * (P2_IB + 1) + lane] = w[i];
+            }
+        }
+        __syncthreads();
+        if (bad) return;  // A is left untouched; INFO tells the caller
+        const int r0 = c0 + P2_IB;  // first row / column of the trailing part
+        if (r0 >= NB) break;
+        // ---- (2) rows below: X[r][j] = sum_{k <= j} A[r][c0 + k] W[j][k]; a warp owns a row, lane = j
+        {
+            const double* Wb = Wd + b * P2_IB * (P2_IB + 1);
+            double wrow[P2_IB];
+#pragma unroll
+            for (int k = 0; k < P2_IB; ++k) wrow[k] = Wb[lane * (P2_IB + 1) + k];  // W[j = lane][k], zero for k > j
+            for (int r = r0 + warp; r < NB; r += WARPS) {
+                const double v = S[r * P2_LD + c0 + lane];
+                double x = 0.0;
+#pragma unroll
+                for (int k = 0; k < P2_IB; ++k) x = fma(__shfl_sync(FULL, v, k), wrow[k], x);
+                S[r * P2_LD + c0 + lane] = x;
+            }
+        }
+        __syncthreads();
+        // ---- (3) trailing lower triangle: A[r][c] -= sum_k X[r][k] X[c][k]; lane owns a column (kept in registers)
+        for (int cc = r0; cc < NB; cc += 32) {
+            const int c = cc + lane;
+            double colv[P2_IB];
+#pragma unroll
+            for (int k = 0; k < P2_IB; ++k) colv[k] = S[c * P2_LD + c0 + k];
+            for (int r = cc + warp; r < NB; r += WARPS) {  // rows >= cc; entries with c > r are skipped
+                const double* xr = S + r * P2_LD + c0;
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < P2_IB; ++k) acc = fma(xr[k], colv[k], acc);
+                if (c <= r) S[r * P2_LD + c] -= acc;
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- L back to global (lower triangle incl. diagonal)
+    for (int e = tid; e < n * n; e += P2_THREADS) {
+        const int r = e / n, c = e - r * n;
+        if (c <= r) A[(int64_t)r * lda + c] = S[r * P2_LD + c];
+    }
+    // ---- inv(L): diagonal blocks are Wd; block (i, j), i > j: W_ij = -W_ii (sum_{k=j}^{i-1} L_ik W_kj),
+    // stored TRANSPOSED in the strict upper part of S: W_ij[t][c] lives at S[32 j + c][32 i + t]
+    constexpr int NBLK = NB / P2_IB;
+    for (int dist = 1; dist < NBLK; ++dist) {
+        const int nprod = NBLK - dist;  // blocks (i, i - dist), i = dist .. NBLK-1
+        // T = sum_k L_ik W_kj
+        for (int o = tid; o < nprod * P2_IB * P2_IB; o += P2_THREADS) {
+            const int p = o / (P2_IB * P2_IB), rc = o - p * P2_IB * P2_IB;
+            const int r = rc / P2_IB, c = rc - r * P2_IB;
+            const int i = dist + p, j = p;
+            double acc = 0.0;
+            for (int k = j; k < i; ++k) {
+                const double* Lik = S + (P2_IB * i + r) * P2_LD + P2_IB * k;
+                if (k == j) {
+                    const double* Wjj = Wd + j * P2_IB * (P2_IB + 1);
+#pragma unroll 8
+                    for (int t = 0; t < P2_IB; ++t) acc = fma(Lik[t], Wjj[t * (P2_IB + 1) + c], acc);
+                } else {
+                    const double* Wkj = S + (P2_IB * j + c) * P2_LD + P2_IB * k;  // transposed storage
+#pragma unroll 8
+                    for (int t = 0; t < P2_IB; ++t) acc = fma(Lik[t], Wkj[t], acc);
+                }
+            }
+            Tm[(p * P2_IB + r) * (P2_IB + 1) + c] = acc;
+        }
+        __syncthreads();
+        // W_ij = -W_ii T
+        for (int o = tid; o < nprod * P2_IB * P2_IB; o += P2_THREADS) {
+            const int p = o / (P2_IB * P2_IB), rc = o - p * P2_IB * P2_IB;
+            const int r = rc / P2_IB, c = rc - r * P2_IB;
+            const int i = dist + p, j = p;
+            const double* Wii = Wd + i * P2_IB * (P2_IB + 1);
+            const double* T = Tm + p * P2_IB * (P2_IB + 1);
+            double acc = 0.0;
+#pragma unroll 8
+            for (int t = 0; t < P2_IB; ++t) acc = fma(Wii[r * (P2_IB + 1) + t], T[t * (P2_IB + 1) + c], acc);  // W_ii[r][t] = 0 for t > r
+            S[(P2_IB * j + c) * P2_LD + P2_IB * i + r] = -acc;
+        }
+        __syncthreads();
+    }
+    for (int e = tid; e < NB * NB; e += P2_THREADS) {
+        const int r = e / NB, c = e - r * NB;
+        double v = 0.0;
+        if (r < n && c <= r) {
+            const int bi = r / P2_IB, bj = c / P2_IB;
+            v = (bi == bj) ? Wd[(bi * P2_IB + (r - bi * P2_IB)) * (P2_IB + 1) + (c - bj * P2_IB)] : S[c * P2_LD + r];
+        }
+        invL[e] = v;
+    }
+}
+
 __global__ void logdet_kernel(const double* L, int64_t ld, int64_t n, double* out) {
     // single CTA, fixed order: deterministic
     __shared__ double red[32];
@@ -120,7 +303,10 @@ static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, in
         const int n = (int)((K0 + W - k0 < NB) ? (K0 + W - k0) : NB);
         double* Akk = A + k0 * ld + k0;
         double* invk = invL + (k0 / NB) * (int64_t)NB * NB;
-        potrf_tile_kernel<<<1, PT_THREADS, smem, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+        if (c->opt_potrf_tile == 2)
+            potrf_tile2_kernel<<<1, P2_THREADS, P2_SMEM, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+        else
+            potrf_tile_kernel<<<1, PT_THREADS, smem, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
         ++c->launches;
         GP_CUDA(c, cudaGetLastError());
         const int64_t m = N - k0 - n;
@@ -149,6 +335,7 @@ static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, in
 int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host) {
     const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     int64_t NBO = c->opt_nbo;
     if (NBO < NB) NBO = NB;
@@ -238,6 +425,7 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
 int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* info_host) {
     const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     (void)col0;
     GP_TRY(factor_panel(c, P, ld, rows, 0, w, invL, smem, c->stream));

@@ -40,6 +40,48 @@ __global__ void k_dmma884(double* out, double a, double b) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// GEMM-shaped register tile, no memory: FM x FN accumulators from FM distinct A and FN distinct B fragments
+// (64 x 32 warp tile = 8 x 4), optionally fed from shared memory like the real main loop.
+template <int FM, int FN, bool LDS>
+__global__ void k_dmma_tile(double* out, double a, double b) {
+    __shared__ double sA[64 * 16], sB[32 * 16];
+    for (int i = threadIdx.x; i < 64 * 16; i += blockDim.x) sA[i] = a + i * 1e-9;
+    for (int i = threadIdx.x; i < 32 * 16; i += blockDim.x) sB[i] = b + i * 1e-9;
+    __syncthreads();
+    double c[FM][FN][2];
+#pragma unroll
+    for (int i = 0; i < FM; ++i)
+#pragma unroll
+        for (int j = 0; j < FN; ++j) { c[i][j][0] = i; c[i][j][1] = j; }
+    const int lane = threadIdx.x & 31, grp = lane >> 2, t4 = lane & 3;
+    double af[FM], bf[FN];
+#pragma unroll
+    for (int i = 0; i < FM; ++i) af[i] = a + i;
+#pragma unroll
+    for (int j = 0; j < FN; ++j) bf[j] = b + j;
+    for (int it = 0; it < ITERS; ++it) {
+        if (LDS) {
+            const int kk = it & 3;
+#pragma unroll
+            for (int i = 0; i < FM; ++i) af[i] = sA[(i * 8 + grp) * 16 + ((((kk * 2 + (t4 >> 1)) ^ ((grp & 3) << 1)) << 1) | (t4 & 1))];
+#pragma unroll
+            for (int j = 0; j < FN; ++j) bf[j] = sB[(j * 8 + grp) * 16 + ((((kk * 2 + (t4 >> 1)) ^ ((grp & 3) << 1)) << 1) | (t4 & 1))];
+        }
+#pragma unroll
+        for (int i = 0; i < FM; ++i)
+#pragma unroll
+            for (int j = 0; j < FN; ++j)
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                             : "+d"(c[i][j][0]), "+d"(c[i][j][1]) : "d"(af[i]), "d"(bf[j]));
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < FM; ++i)
+#pragma unroll
+        for (int j = 0; j < FN; ++j) s += c[i][j][0] + c[i][j][1];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <int NACC>
 __global__ void k_dmma1688(double* out, double a, double b) {
     double c[NACC][4];
@@ -125,6 +167,9 @@ int main() {
         run("dfma x16", [&] { k_dfma<<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 16 * 2.0, blocks, thr);
         run("dmma m8n8k4 x8", [&] { k_dmma884<8><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 8 * 512.0 / 32, blocks, thr);
         run("dmma m8n8k4 x32", [&] { k_dmma884<32><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 32 * 512.0 / 32, blocks, thr);
+        run("dmma tile 8x4 regs", [&] { k_dmma_tile<8, 4, false><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 32 * 512.0 / 32, blocks, thr);
+        run("dmma tile 8x4 lds", [&] { k_dmma_tile<8, 4, true><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 32 * 512.0 / 32, blocks, thr);
+        run("dmma tile 8x2 lds", [&] { k_dmma_tile<8, 2, true><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 16 * 512.0 / 32, blocks, thr);
         run("dmma m16n8k4 x16", [&] { k_dmma1684<16><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 16 * 1024.0 / 32, blocks, thr);
         run("dmma m16n8k8 x16", [&] { k_dmma1688<16><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 16 * 2048.0 / 32, blocks, thr);
         run("dmma m16n8k16 x16", [&] { k_dmma16816<16><<<blocks, thr>>>(out, 1.0000001, 1e-9); }, 16 * 4096.0 / 32, blocks, thr);
