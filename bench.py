@@ -307,10 +307,14 @@ def run_gpu(args):
                     "matches_device_run": e2e_ok},
             "gpu_launches": total_launches,
             "roofline": {
-                "kernel": "dgemm_kernel<128,64,NT> (SYRK trailing update of the blocked Cholesky, DMMA.8x8x4)",
+                "kernel": "dgemm_kernel<128,64,64,16,NT,3 stages> (SYRK trailing update of the blocked Cholesky, "
+                          "DMMA.8x8x4, 16 warps/SM)",
                 "bound": "tensor", "achieved": tb_flops / tb_ms * 1e-9 if tb_ms else None, "peak": FP64_PEAK_TFLOPS,
                 "unit": "TFLOP/s", "frac": (tb_flops / tb_ms * 1e-9 / FP64_PEAK_TFLOPS) if tb_ms else None,
                 "traffic": TRAFFIC_TB_BYTES_PER_LAUNCH,
+                "traffic_note": "ncu capture of the largest launch T^b(0) (31744^2/2 by K=1024, 28.62 ms): 7.61 GB read "
+                                "+ 3.76 GB written against 7.79 GB algorithmic (panel + C read + C write); "
+                                "profiles/r01b_ncu_summary.md",
                 "launches": tb_launches, "avg_launch_ms": tb_ms / tb_launches if tb_launches else None,
                 "share_of_step": tb_ms / (elapsed_ms) if elapsed_ms else None,
                 "peak_source": "FP64 is absent from MEASURED_PEAKS.json; 37.1 = measured DMMA issue rate on this pool "
@@ -336,9 +340,9 @@ def run_gpu(args):
     return 0
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per trailing-update launch from the ncu --set full capture
-# (profiles/); None until a capture of the current kernel has been read.
-TRAFFIC_TB_BYTES_PER_LAUNCH = None
+# dram__bytes_read.sum + dram__bytes_write.sum of the trailing-update launch captured with ncu --set full
+# (profiles/r01b_ncu_summary.md: T^b(0) at N=32768, NBO=1024: 7.608593 GB + 3.756411 GB).
+TRAFFIC_TB_BYTES_PER_LAUNCH = 7.608593e9 + 3.756411e9
 
 
 def residual_check(torch, gpr_b200, h, Xd, Yd, N, dev):
@@ -430,7 +434,8 @@ def run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier, ma
     return out
 
 
-TRAFFIC_GEMV_BYTES_PER_LAUNCH = None
+# profiles/r01b_ncu_summary.md: gemv_t_kernel at C2, 25.77 GB read (= 8NM) + the M-vector written.
+TRAFFIC_GEMV_BYTES_PER_LAUNCH = 25.77e9 + 8.0 * 786432
 
 
 def run_loglik(torch, gpr_b200, local_rank, N=16384, iters=3):

@@ -63,7 +63,8 @@ struct Ctx {
     double logdet = 0.0;
 
     int64_t opt_gram_lower_only = 1;
-    int64_t opt_nbo = 1024;       // outer (trailing-update) block of the two-level Cholesky
+    int64_t opt_nbo = 0;          // outer (trailing-update) block of the two-level Cholesky; 0 = auto (512 / 1024)
+    int64_t opt_chol_left = 0;    // left-looking outer loop (long-K column updates): measured slower, see potrf.cu
     int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs
     int64_t opt_potrf_tile = 2;    // 2: blocked register/shuffle diagonal-tile kernel, 1: unblocked shared-memory kernel
     int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu

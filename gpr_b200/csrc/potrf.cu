@@ -327,6 +327,104 @@ static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, in
     return 0;
 }
 
+// Left-looking outer loop (option "chol_left"): block column J (width NBO) is brought up to date with ALL earlier
+// panels in long-K GEMMs and is written once, instead of every trailing tile being read-modified-written once per
+// panel as in the right-looking form below (the K = 1024 epilogue cost ~8 % of the tensor pipe in the round-1 ncu
+// capture). The update of column J is split by what it depends on:
+//     G_a(J): K range = panels 0 .. J-2   (independent of the panel being factored right now)
+//     G_b(J): K range = panel J-1         (the only part on the critical path)
+//   main stream : ... G_a(J) | wait panel(J-1) | G_b(J) | G_a(J+1) | wait panel(J) | G_b(J+1) ...
+//   panel stream:                               wait G_b(J) | panel(J)
+// so panel(J) (latency-bound) always runs under G_a(J+1) (the bulk of the flops, K up to N).
+// MEASURED (B200, tools/left_ab.py): 404 ms vs 384 ms right-looking at N = 32768, 1266 vs 1223 ms at N = 49152: the
+// column GEMMs have only (N - J0) / 128 x 16 tiles (3-4 waves of 296 resident CTAs, wave-quantisation loss) and the
+// G_b -> panel chain is fully serial. Kept as an option (default off); the right-looking form is the product path.
+static int update_column(Ctx* c, double* A, int64_t ld, int64_t N, int64_t J0, int64_t W, int64_t k_begin, int64_t k_end,
+                         cudaStream_t st) {
+    const int64_t K = k_end - k_begin;
+    if (K <= 0) return 0;
+    // top W x W block: symmetric, lower tiles only
+    GemmArgs t{};
+    t.A = A + J0 * ld + k_begin; t.lda = ld; t.B = t.A; t.ldb = ld; t.C = A + J0 * ld + J0; t.ldc = ld;
+    t.M = (int)W; t.N = (int)W; t.K = (int)K; t.alpha = -1.0; t.beta = 1.0; t.lower = 1;
+    GP_TRY(gemm(c, GEMM_NT, t, st));
+    const int64_t m = N - J0 - W;
+    if (m > 0) {
+        GemmArgs b{};
+        b.A = A + (J0 + W) * ld + k_begin; b.lda = ld; b.B = A + J0 * ld + k_begin; b.ldb = ld;
+        b.C = A + (J0 + W) * ld + J0; b.ldc = ld;
+        b.M = (int)m; b.N = (int)W; b.K = (int)K; b.alpha = -1.0; b.beta = 1.0;
+        GP_TRY(gemm(c, GEMM_NT, b, st));
+    }
+    return 0;
+}
+
+static int potrf_left(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int64_t NBO, size_t smem) {
+    cudaStream_t sm = c->stream, sp = c->panel_stream ? c->panel_stream : c->stream;
+    const int64_t nJ = (N + NBO - 1) / NBO;
+    std::vector<cudaEvent_t> ev_panel((size_t)nJ, nullptr), ev_gb((size_t)nJ, nullptr);
+    int rc = 0;
+    auto mk = [&](cudaEvent_t& e) { return cudaEventCreateWithFlags(&e, cudaEventDisableTiming); };
+    cudaEvent_t ev_start = nullptr;
+    mk(ev_start);
+    cudaEventRecord(ev_start, sm);  // panel 0 waits for everything queued so far (the Gram build)
+    cudaStreamWaitEvent(sp, ev_start, 0);
+    rc = factor_panel(c, A, ld, N, 0, (N < NBO) ? N : NBO, invL, smem, sp);
+    mk(ev_panel[0]);
+    cudaEventRecord(ev_panel[0], sp);
+    std::vector<cudaEvent_t> pev;
+    std::vector<double> pflops;
+    for (int64_t J = 1; J < nJ && rc == 0; ++J) {
+        const int64_t J0 = J * NBO;
+        const int64_t W = (N - J0 < NBO) ? (N - J0) : NBO;
+        if (J >= 2) {
+            cudaStreamWaitEvent(sm, ev_panel[(size_t)J - 2], 0);
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (c->opt_profile) {
+                cudaEventCreate(&e0);
+                cudaEventCreate(&e1);
+                cudaEventRecord(e0, sm);
+            }
+            rc = update_column(c, A, ld, N, J0, W, 0, J0 - NBO, sm);
+            if (c->opt_profile) {
+                cudaEventRecord(e1, sm);
+                pev.push_back(e0);
+                pev.push_back(e1);
+                pflops.push_back((double)(J0 - NBO) * ((double)W * (W + 1) + 2.0 * (double)(N - J0 - W) * W));
+            }
+            if (rc) break;
+        }
+        cudaStreamWaitEvent(sm, ev_panel[(size_t)J - 1], 0);
+        rc = update_column(c, A, ld, N, J0, W, J0 - NBO, J0, sm);
+        if (rc) break;
+        mk(ev_gb[(size_t)J]);
+        cudaEventRecord(ev_gb[(size_t)J], sm);
+        cudaStreamWaitEvent(sp, ev_gb[(size_t)J], 0);
+        rc = factor_panel(c, A, ld, N, J0, W, invL, smem, sp);
+        mk(ev_panel[(size_t)J]);
+        cudaEventRecord(ev_panel[(size_t)J], sp);
+    }
+    if (ev_panel[(size_t)nJ - 1]) cudaStreamWaitEvent(sm, ev_panel[(size_t)nJ - 1], 0);  // rejoin the main stream
+    if (c->opt_profile) {
+        c->prof_tb_ms = c->prof_tb_flops = c->prof_tb_launches = 0.0;
+        for (size_t i = 0; i + 1 < pev.size(); i += 2) {
+            float ms = 0.f;
+            cudaEventSynchronize(pev[i + 1]);
+            if (cudaEventElapsedTime(&ms, pev[i], pev[i + 1]) == cudaSuccess) {
+                c->prof_tb_ms += ms;
+                c->prof_tb_flops += pflops[i / 2];
+                c->prof_tb_launches += 1.0;
+            }
+            cudaEventDestroy(pev[i]);
+            cudaEventDestroy(pev[i + 1]);
+        }
+    }
+    for (auto e : ev_panel) if (e) cudaEventDestroy(e);
+    for (auto e : ev_gb) if (e) cudaEventDestroy(e);
+    cudaEventDestroy(ev_start);
+    return rc;
+}
+
 // Two-level right-looking Cholesky with one-panel look-ahead:
 //   main stream : ... T^b(K-1) | wait panel(K) | T^a(K) | T^b(K) ...
 //   panel stream:      wait T^a(K-1) | panel(K)
@@ -338,8 +436,17 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     int64_t NBO = c->opt_nbo;
+    if (NBO <= 0) NBO = (N <= 20480) ? 512 : 1024;  // measured on B200: 512 wins up to N = 16384, 1024 from 32768
     if (NBO < NB) NBO = NB;
     NBO = NBO / NB * NB;
+    if (c->opt_chol_left && c->panel_stream && N > 2 * NBO) {
+        GP_TRY(potrf_left(c, A, ld, N, invL, NBO, smem));
+        if (info_host) {
+            GP_CUDA(c, cudaMemcpyAsync(info_host, c->dInfo, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+            GP_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+        return 0;
+    }
     const bool la = c->opt_lookahead && c->panel_stream && N > NBO;
     cudaStream_t sm = c->stream, sp = la ? c->panel_stream : c->stream;
     cudaEvent_t ev_panel = nullptr, ev_ta = nullptr;
