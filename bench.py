@@ -531,7 +531,7 @@ def run_cpu_baseline():
                     "sample": "unavailable: oracle/_ref/libgpr_ref.so missing"}
         threads = os.cpu_count() or 1
         os.environ["OMP_NUM_THREADS"] = str(threads)
-        N = 6144
+        N = 10240  # ~10 s on 16 cores; throughput of dgetrf/dgetri is flat in N from here on
         time_reference_learn(1024, threads)
         dt, _ = time_reference_learn(N, threads)
         return {"value": learn_flops(N, C3_M) / dt * 1e-12, "unit": "TFLOP/s", "cores": threads, "kind": "reference",
