@@ -57,6 +57,23 @@ _PROTOS = {
     "gprb200_dgram": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_loglik": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gprb200_quadform": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gprb200_pca_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "gprb200_pca_destroy": (C.c_int, [C.c_void_p]),
+    "gprb200_pca_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
+    "gprb200_pca_fit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64]),
+    "gprb200_pca_fit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64]),
+    "gprb200_pca_set": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64]),
+    "gprb200_pca_get": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gprb200_pca_dims": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "gprb200_pca_get_stat": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_double)]),
+    "gprb200_pca_project": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
+    "gprb200_pca_project_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64]),
+    "gprb200_pca_reconstruct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
+    "gprb200_pca_reconstruct_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_int64, C.c_void_p,
+                                              C.c_int64]),
+    "gprb200_predict_reconstruct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "gprb200_predict_reconstruct_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                                  C.c_void_p, C.c_int64]),
 }
 
 WANT_CORE = 1

@@ -35,7 +35,6 @@ __global__ void deriv_lhs_kernel(const double* x, const double* X, const double*
 }  // namespace gprb200
 
 // the opaque C handle is the context itself
-struct gprb200_ctx : gprb200::Ctx {};
 
 static thread_local std::string g_create_error;
 

@@ -28,6 +28,10 @@ struct GemmArgs {
     int M, N, K;
     double alpha, beta;
     int lower;  // 1: only tiles that intersect {row >= col} are computed (SYRK trailing update)
+    // batch > 1: blockIdx.y selects operand set z with A + z*sA, B + z*sB, C + z*sC (split-K partial products
+    // of the PCA Gram, pca.cu). 0 and 1 both mean a single GEMM.
+    int batch;
+    int64_t sA, sB, sC;
 };
 
 enum GemmForm { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };
@@ -134,3 +138,6 @@ int rowdot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, i
 int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out);
 
 }  // namespace gprb200
+
+// the opaque handle of include/gprb200.h
+struct gprb200_ctx : gprb200::Ctx {};

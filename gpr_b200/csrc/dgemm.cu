@@ -179,8 +179,9 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
     const int grp = lane >> 2, t4 = lane & 3;
 
-    const double* Abase = AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0);
-    const double* Bbase = BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0);
+    const int64_t z = blockIdx.y;  // batch index (0 for a single GEMM; the strides are then unused)
+    const double* Abase = (AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0)) + z * g.sA;
+    const double* Bbase = (BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0)) + z * g.sB;
     const int mrem = g.M - m0, nrem = g.N - n0;
     const int nk = (g.K + BK - 1) / BK;
 
@@ -258,7 +259,7 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     for (int i = 0; i < FM; ++i) {
         const int row = m0 + wm0 + i * 8 + grp;
         if (row >= g.M) continue;
-        double* crow = g.C + (int64_t)row * g.ldc;
+        double* crow = g.C + z * g.sC + (int64_t)row * g.ldc;
 #pragma unroll
         for (int j = 0; j < FN; ++j) {
             const int col = n0 + wn0 + j * 8 + t4 * 2;
@@ -299,7 +300,7 @@ static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
         grid = tm * tn;
     }
     if (grid <= 0) return 0;
-    kern<<<(unsigned)grid, THREADS, SMEM, stream>>>(g, (int)tm, (int)tn);
+    kern<<<dim3((unsigned)grid, (unsigned)(g.batch > 1 ? g.batch : 1)), THREADS, SMEM, stream>>>(g, (int)tm, (int)tn);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     return 0;
@@ -313,7 +314,8 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     // few right-hand sides: HBM-bound streaming kernels instead of a mostly empty tensor-core tile (skinny.cu).
     // In-place use (C aliasing B: the diagonal-block step Z_k = inv(L_kk) B_k) keeps the tile kernel, whose CTA
     // reads all of its B columns before it writes.
-    if (!g.lower && g.N <= 8 && (form == GEMM_NN || form == GEMM_TN) && g.C != g.B && g.C != g.A && c->opt_skinny)
+    if (!g.lower && g.N <= 8 && g.batch <= 1 && (form == GEMM_NN || form == GEMM_TN) && g.C != g.B && g.C != g.A &&
+        c->opt_skinny)
         return gemm_skinny(c, form, g, stream);
     if (!aligned16(g.A) || !aligned16(g.B) || !aligned16(g.C) || (g.lda & 1) || (g.ldb & 1) || (g.ldc & 1))
         return fail(c, -2, "gemm: operands must be 16-byte aligned with even leading dimensions");

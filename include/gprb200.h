@@ -183,6 +183,45 @@ int gprb200_loglik(gprb200_handle h, int mode, double* value, double* grad, doub
 /* q[k] = y_k^T (K + sigma^2 I)^-1 y_k, the data-fit term of include/Likelihood.h:175 (M values) */
 int gprb200_quadform(gprb200_handle h, double* q);
 
+/* ---- PCA (reference include/PCA.h) --------------------------------------
+ * The reference's PCA<T> maps the GP's predicted principal weights to the displacement field, once per frame
+ * (include/DataParser.h:471-495, :211-286). Data matrices are D x n row-major, ONE SAMPLE PER COLUMN, exactly the
+ * MatrixType the reference passes. A PCA object lives on the device and stream of the handle it was created from and
+ * must be destroyed before that handle. Singular vectors are defined up to sign (as with Eigen's BDCSVD). */
+typedef struct gprb200_pca* gprb200_pca_handle;
+int gprb200_pca_create(gprb200_handle h, gprb200_pca_handle* p);
+int gprb200_pca_destroy(gprb200_pca_handle p);
+/* "passes" (default 2): Gram/Jacobi passes of the fit; the second restores the accuracy the first Gram squares away. */
+int gprb200_pca_set_option(gprb200_pca_handle p, const char* name, int64_t value);
+/* PCA(MatrixType& X, int nFeatures), include/PCA.h:33-49: mean = X.rowwise().mean(), thin SVD of the mean-free data,
+ * sigma = singular values / sqrt(n), U (D x n). n <= 8192, n <= D. */
+int gprb200_pca_fit(gprb200_pca_handle p, const double* X, int64_t D, int64_t n, int64_t n_features);
+int gprb200_pca_fit_dev(gprb200_pca_handle p, const double* dX, int64_t ldx, int64_t D, int64_t n, int64_t n_features);
+/* PCA(std::string path, int nFeatures), include/PCA.h:51-65, after the three ReadMatrix calls (Mean/Sigma/U.bin). */
+int gprb200_pca_set(gprb200_pca_handle p, const double* mean, const double* sigma, const double* U, int64_t D, int64_t n,
+                    int64_t n_features);
+/* GetMean / GetEigenvalues / GetMatrixU (include/PCA.h:71-81); any pointer may be NULL. */
+int gprb200_pca_get(gprb200_pca_handle p, double* mean, double* sigma, double* U);
+int gprb200_pca_dims(gprb200_pca_handle p, int64_t* D, int64_t* n, int64_t* n_features);
+int gprb200_pca_get_stat(gprb200_pca_handle p, const char* name, double* out); /* "fit_ms", "sweeps" */
+/* DimensionalityReduction / DimensionalityReductionFast (include/PCA.h:92-108): F = (U diag(1/sigma))^T (X - mean),
+ * first rows_out rows (rows_out <= n; rows_out <= nFeatures streams the compact basis). X: D x T, F: rows_out x T. */
+int gprb200_pca_project(gprb200_pca_handle p, const double* X, int64_t T, int64_t rows_out, double* F);
+int gprb200_pca_project_dev(gprb200_pca_handle p, const double* dX, int64_t ldx, int64_t T, int64_t rows_out, double* dF,
+                            int64_t ldf);
+/* GetReconstruction (include/PCA.h:110-115): Xout (D x T) = (U diag(sigma))[:, :nFeatures] W + mean,
+ * W: nFeatures x T. _dev: transposed != 0 reads W as T x nFeatures (the layout Predict writes). */
+int gprb200_pca_reconstruct(gprb200_pca_handle p, const double* W, int64_t n_weights, int64_t T, double* Xout);
+int gprb200_pca_reconstruct_dev(gprb200_pca_handle p, const double* dW, int64_t ldw, int transposed, int64_t n_weights,
+                                int64_t T, double* dOut, int64_t ldo);
+/* gp->Predict(v) for every frame (apps/GaussianProcessPredict.cpp:188-203) followed by inversePca()
+ * (include/DataParser.h:471-495) without leaving the device. Xs: T x d; fields: D x T (may be NULL);
+ * weights: T x M predicted principal weights (may be NULL). The GP must have M = nFeatures outputs. */
+int gprb200_predict_reconstruct(gprb200_handle h, gprb200_pca_handle p, const double* Xs, int64_t T, double* fields,
+                                double* weights);
+int gprb200_predict_reconstruct_dev(gprb200_handle h, gprb200_pca_handle p, const double* dXs, int64_t T, double* dFields,
+                                    int64_t ldo, double* dWeights, int64_t ldw);
+
 #ifdef __cplusplus
 }
 #endif

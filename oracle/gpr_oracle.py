@@ -294,3 +294,43 @@ class OracleGP:
             for p in range(P):
                 J[i, p] = 0.5 * np.trace(A @ D[p * N:(p + 1) * N])
         return J
+
+
+# ---------------------------------------------------------------------------------------------------
+# PCA: restatement of include/PCA.h. X is D x n with one sample per column.
+# ---------------------------------------------------------------------------------------------------
+class PCAOracle:
+    """include/PCA.h:33-49 (fit), :92-108 (project), :110-115 (reconstruct), :117-124 (explained variance).
+    numpy's svd is LAPACK gesdd, the same divide-and-conquer family as Eigen::BDCSVD; singular vectors are
+    defined up to sign, so comparisons are made on sign-invariant quantities."""
+
+    def __init__(self, X=None, n_features=0, mean=None, sigma=None, U=None):
+        self.n_features = int(n_features)
+        if X is not None:
+            X = np.asarray(X, dtype=np.float64)
+            self.mean = X.mean(axis=1)                                   # PCA.h:37  X.rowwise().mean()
+            Xc = X - self.mean[:, None]                                  # :38
+            U, s, _ = np.linalg.svd(Xc, full_matrices=False)             # :41  BDCSVD, ComputeThinU
+            self.sigma = s / np.sqrt(X.shape[1])                         # :44
+            self.U = U                                                   # :45
+        else:
+            self.mean, self.sigma, self.U = (np.asarray(a, dtype=np.float64) for a in (mean, sigma, U))
+            self.mean, self.sigma = self.mean.ravel(), self.sigma.ravel()
+        with np.errstate(divide="ignore"):
+            self.basis = self.U / self.sigma[None, :]                    # :46  U * sigma.asDiagonal().inverse()
+        self.basis_inverse = (self.U * self.sigma[None, :])[:, :self.n_features]   # :47-48
+
+    def project(self, X, fast=False):
+        Xc = np.asarray(X, dtype=np.float64) - self.mean[:, None]        # :93
+        if fast:
+            return self.basis[:, :self.n_features].T @ Xc                # :68, :102-106
+        return self.basis.T @ Xc                                         # :94 (`nFeatures << rows` keeps every row)
+
+    def reconstruct(self, W):
+        return self.basis_inverse @ np.asarray(W, dtype=np.float64) + self.mean[:, None]   # :110-115
+
+    def explained_variance(self):
+        """The intent of :117-124 (cumulative sigma, normalised). The reference indexes the VECTOR m_sigma as
+        (i, i), which reads out of bounds for i >= 1 in a column vector; not reproduced."""
+        c = np.cumsum(self.sigma)
+        return c / c[-1]

@@ -222,3 +222,67 @@ class RefGP:
         v = np.empty(self.M)
         _ck(lib().ref_lik_value(self.h, _p(v)))
         return v
+
+
+class RefPCA:
+    """The reference's PCA<double> (include/PCA.h) through oracle/_ref. X is D x n, one sample per column."""
+
+    def __init__(self, X=None, n_features=0, prefix=None):
+        L = lib()
+        L.ref_pca_fit.restype = C.c_void_p
+        L.ref_pca_fit.argtypes = [C.c_void_p, C.c_long, C.c_long, C.c_int]
+        L.ref_pca_load.restype = C.c_void_p
+        L.ref_pca_load.argtypes = [C.c_char_p, C.c_int]
+        L.ref_pca_free.argtypes = [C.c_void_p]
+        L.ref_pca_get.argtypes = [C.c_void_p] * 4
+        L.ref_pca_write.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_pca_project.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_void_p, C.c_void_p]
+        L.ref_pca_reconstruct.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_void_p]
+        self.n_features = int(n_features)
+        if prefix is not None:
+            self.p = L.ref_pca_load(str(prefix).encode(), self.n_features)
+            if not self.p:
+                raise RefError(L.ref_last_error().decode())
+            self.D = self.n = None
+        else:
+            X = _f(X)
+            self.D, self.n = X.shape
+            self.p = L.ref_pca_fit(_p(X), self.D, self.n, self.n_features)
+            if not self.p:
+                raise RefError(L.ref_last_error().decode())
+
+    def close(self):
+        if self.p:
+            lib().ref_pca_free(self.p)
+            self.p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def get(self):
+        mean, sigma, U = np.empty(self.D), np.empty(self.n), np.empty((self.D, self.n))
+        _ck(lib().ref_pca_get(self.p, _p(mean), _p(sigma), _p(U)))
+        return mean, sigma, U
+
+    def write(self, prefix):
+        _ck(lib().ref_pca_write(self.p, str(prefix).encode()))
+
+    def project(self, X, fast=False):
+        X = _f(X)
+        D, ncols = X.shape
+        out = np.empty((max(self.n or 0, self.n_features, 1) if not fast else self.n_features, ncols))
+        if not fast and self.n is None:
+            raise RefError("project(fast=False) needs the number of modes; use a fitted object")
+        rows = C.c_long()
+        _ck(lib().ref_pca_project(self.p, _p(X), D, ncols, int(bool(fast)), _p(out), C.byref(rows)))
+        return out[:rows.value]
+
+    def reconstruct(self, W, D=None):
+        W = _f(W)
+        nF, ncols = W.shape
+        out = np.empty((D or self.D, ncols))
+        _ck(lib().ref_pca_reconstruct(self.p, _p(W), nF, ncols, _p(out)))
+        return out

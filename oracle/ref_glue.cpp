@@ -13,6 +13,7 @@
 #include <string>
 
 #include "lib/GaussianProcess.cpp"  // -I/root/reference
+#include "include/PCA.h"          // the reference's PCA, BDCSVD -> LAPACK dgesdd in eigen_lite
 
 // ---- LAPACK: the reference declares the un-prefixed Fortran symbols; scipy's OpenBLAS exports them
 //      with a scipy_ prefix (LP64).
@@ -262,6 +263,64 @@ int ref_chol_invert(double* A, int N) {
         Mat M(N, N);
         std::memcpy(M.data(), A, sizeof(double) * N * N);
         from_mat(gpr::lapack::chol_invert<double>(M), A);
+    });
+}
+
+
+// ---- PCA (include/PCA.h) ----------------------------------------------------------------------------
+// X is D x n row-major (one sample per column, as DataParser builds it). Outputs: mean (D), sigma (n),
+// U (D x n row-major).
+void* ref_pca_fit(const double* X, long D, long n, int nFeatures) {
+    void* out = nullptr;
+    guard([&] {
+        Mat M(D, n);
+        std::memcpy(M.data(), X, sizeof(double) * D * n);
+        out = new PCA<double>(M, nFeatures);
+    });
+    return out;
+}
+void ref_pca_free(void* p) { delete static_cast<PCA<double>*>(p); }
+int ref_pca_get(void* p, double* mean, double* sigma, double* U) {
+    return guard([&] {
+        PCA<double>* pca = static_cast<PCA<double>*>(p);
+        if (mean) from_mat(pca->GetMean(), mean);
+        if (sigma) from_mat(pca->GetEigenvalues(), sigma);
+        if (U) from_mat(pca->GetMatrixU(), U);
+    });
+}
+int ref_pca_write(void* p, const char* prefix) {
+    return guard([&] { static_cast<PCA<double>*>(p)->WriteMatricesToFile(prefix); });
+}
+void* ref_pca_load(const char* prefix, int nFeatures) {
+    void* out = nullptr;
+    guard([&] { out = new PCA<double>(std::string(prefix), nFeatures); });
+    return out;
+}
+// features = basis^T (X - mean): rows_out x ncols, rows_out = n (all modes), or nFeatures with fast != 0
+int ref_pca_project(void* p, const double* X, long D, long ncols, int fast, double* out, long* rows_out) {
+    return guard([&] {
+        PCA<double>* pca = static_cast<PCA<double>*>(p);
+        Mat M(D, ncols);
+        std::memcpy(M.data(), X, sizeof(double) * D * ncols);
+        Mat F;
+        if (fast) {
+            pca->PrecomputeTranspose();
+            F = pca->DimensionalityReductionFast(M);
+        } else {
+            F = pca->DimensionalityReduction(M);
+        }
+        *rows_out = F.rows();
+        from_mat(F, out);
+    });
+}
+// X = basisInverse[:, :nFeatures] W + mean: W is nFeatures x ncols, out D x ncols
+int ref_pca_reconstruct(void* p, const double* W, long nF, long ncols, double* out) {
+    return guard([&] {
+        PCA<double>* pca = static_cast<PCA<double>*>(p);
+        Mat Wm(nF, ncols);
+        std::memcpy(Wm.data(), W, sizeof(double) * nF * ncols);
+        Mat R = pca->GetReconstruction(Wm);
+        from_mat(R, out);
     });
 }
 

@@ -33,3 +33,15 @@ def rel_err(a, b):
     b = np.asarray(b, dtype=np.float64)
     den = max(np.max(np.abs(b)), 1e-300)
     return float(np.max(np.abs(a - b)) / den)
+
+
+def make_pca_data(D, n, rank=12, decay=1e-3, noise=1e-4, seed=0, offset=2.5):
+    """D x n data matrix, one sample per column: `rank` smooth modes with geometrically decaying amplitudes
+    (1 .. decay), white noise at `noise`, and a non-zero mean; the shape of a displacement-field training set
+    (include/DataParser.h:536-613) at test size."""
+    rng = np.random.default_rng(seed)
+    grid = np.linspace(0.0, 1.0, D)
+    modes = np.stack([np.sin((k + 1) * np.pi * grid + 0.3 * k) for k in range(rank)], axis=1)
+    amp = np.geomspace(1.0, decay, rank)
+    X = modes @ (rng.standard_normal((rank, n)) * amp[:, None]) + noise * rng.standard_normal((D, n))
+    return X + offset * np.cos(3.0 * grid)[:, None]
