@@ -102,6 +102,9 @@ public:
     void SetDevice(int device);
     // milliseconds of the last Gram / Cholesky / solve / inverse / predict phases (CUDA events)
     std::vector<double> GetPhaseMilliseconds() const;
+    // The gprb200_handle (include/gprb200.h) this model lives on, initialised and in sync with the host state.
+    // Lets device-side companions (PCA.h: fused Predict -> GetReconstruction) work on the same GPU and stream.
+    void* GetDeviceHandle();
 
     virtual void Save(std::string prefix);
     virtual void Load(std::string prefix);

@@ -282,6 +282,12 @@ TScalarType GaussianProcess<TScalarType>::GetCredibleInterval(const VectorType& 
 }
 
 template <class TScalarType>
+void* GaussianProcess<TScalarType>::GetDeviceHandle() {
+    Initialize();
+    return Device().h;
+}
+
+template <class TScalarType>
 std::vector<double> GaussianProcess<TScalarType>::GetPhaseMilliseconds() const {
     std::vector<double> ms(GPRB200_T_COUNT, 0.0);
     if (m_Device) gprb200_phase_ms(m_Device->h, ms.data());

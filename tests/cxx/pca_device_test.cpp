@@ -1,0 +1,169 @@
+// GPU checks of the C++ PCA<T> (gpr_b200/cxx/include/PCA.h) over libgprb200.so (needs a B200).
+// The reference has no PCA test program; the known answers here are analytic:
+//   P1 data built from exactly orthogonal DCT modes u_k (over the D voxels) and mean-free orthogonal DCT coefficient
+//      vectors c_k (over the n samples) with amplitudes a_k: the thin SVD of the mean-free data is known in closed form,
+//      sigma_k = a_k |u_k| |c_k| / sqrt(n) (include/PCA.h:44), U_k = +-u_k / |u_k|, mean = the constant offset field
+//   P2 DimensionalityReductionFast / GetReconstruction round trip and basis^T basisInverse = I     PCA.h:92-115
+//   P3 WriteMatricesToFile -> PCA(path, nFeatures) reproduces the projections bit for bit            PCA.h:51-65, :126-134
+//   P4 PredictReconstruction(gp, Xs) == GetReconstruction(Predict(x)^T) column by column            (additive API)
+//   P5 float instantiation
+#include <cmath>
+#include <cstdio>
+#include <iostream>
+#include <memory>
+#include <string>
+
+#include "GaussianProcess.h"
+#include "Kernel.h"
+#include "PCA.h"
+
+using namespace gpr;
+
+static int failures = 0;
+#define EXPECT(cond, what)                                                   \
+    do {                                                                     \
+        if (!(cond)) {                                                       \
+            ++failures;                                                      \
+            std::cout << "[failed] " << what << " (" #cond ")" << std::endl; \
+        } else {                                                             \
+            std::cout << "[passed] " << what << std::endl;                   \
+        }                                                                    \
+    } while (0)
+
+static const double kPi = 3.14159265358979323846;
+
+template <class T>
+struct Synth {
+    typedef typename GaussianProcess<T>::MatrixType Mat;
+    long D, n, r;
+    Mat X;
+    std::vector<double> sigma;  // expected, descending
+    Mat Uexp;                   // D x r, unit columns
+    std::vector<double> mean;
+    Synth(long D_, long n_, long r_) : D(D_), n(n_), r(r_), X(D_, n_), sigma((size_t)r_), Uexp(D_, r_), mean((size_t)D_) {
+        for (long i = 0; i < D; ++i) mean[(size_t)i] = 1.5 + std::cos(3.0 * i / (double)D);
+        for (long i = 0; i < D; ++i)
+            for (long j = 0; j < n; ++j) X(i, j) = (T)mean[(size_t)i];
+        for (long k = 0; k < r; ++k) {
+            const double a = 4.0 * std::pow(0.45, (double)k);
+            double un = 0, cn = 0;
+            for (long i = 0; i < D; ++i) { const double u = std::cos(kPi * (k + 2) * (i + 0.5) / D); un += u * u; }
+            for (long j = 0; j < n; ++j) { const double c = std::cos(kPi * (k + 1) * (j + 0.5) / n); cn += c * c; }
+            un = std::sqrt(un); cn = std::sqrt(cn);
+            sigma[(size_t)k] = a * un * cn / std::sqrt((double)n);
+            for (long i = 0; i < D; ++i) {
+                const double u = std::cos(kPi * (k + 2) * (i + 0.5) / D);
+                Uexp(i, k) = (T)(u / un);
+                for (long j = 0; j < n; ++j) X(i, j) += (T)(a * u * std::cos(kPi * (k + 1) * (j + 0.5) / n));
+            }
+        }
+    }
+};
+
+template <class T>
+double MaxAbsDiff(const typename GaussianProcess<T>::MatrixType& A, const typename GaussianProcess<T>::MatrixType& B) {
+    double m = 0;
+    for (long i = 0; i < (long)A.rows(); ++i)
+        for (long j = 0; j < (long)A.cols(); ++j) m = std::max(m, std::fabs((double)A(i, j) - (double)B(i, j)));
+    return m;
+}
+
+template <class T>
+void RunAnalytic(const char* tag, double tol) {
+    typedef typename GaussianProcess<T>::MatrixType Mat;
+    typedef typename GaussianProcess<T>::VectorType Vec;
+    const long D = 3000, n = 24, r = 6;
+    Synth<T> s(D, n, r);
+    PCA<T> pca(s.X, (int)r);
+    Vec sig = pca.GetEigenvalues();
+    Vec mean = pca.GetMean();
+    Mat U = pca.GetMatrixU();
+    double es = 0, em = 0, eu = 0;
+    for (long k = 0; k < r; ++k) es = std::max(es, std::fabs((double)sig[k] / s.sigma[(size_t)k] - 1.0));
+    for (long i = 0; i < D; ++i) em = std::max(em, std::fabs((double)mean[i] - s.mean[(size_t)i]));
+    for (long k = 0; k < r; ++k) {
+        double dot = 0;
+        for (long i = 0; i < D; ++i) dot += (double)U(i, k) * (double)s.Uexp(i, k);
+        eu = std::max(eu, std::fabs(std::fabs(dot) - 1.0));
+    }
+    EXPECT(es <= tol, std::string(tag) + " P1 sigma_k = a_k |u_k| |c_k| / sqrt(n)");
+    EXPECT(em <= tol * 10, std::string(tag) + " P1 mean field");
+    EXPECT(eu <= tol, std::string(tag) + " P1 U_k = +- u_k");
+    EXPECT((double)sig[r] <= 1e-6 * (double)sig[0], std::string(tag) + " P1 rank: modes beyond r vanish");
+
+    Mat F = pca.DimensionalityReductionFast(s.X);
+    Mat back = pca.GetReconstruction(F);
+    EXPECT(MaxAbsDiff<T>(back, s.X) <= tol * 50, std::string(tag) + " P2 reconstruct(project(X)) == X for rank-r data");
+    Mat W(r, 2);
+    for (long k = 0; k < r; ++k) { W(k, 0) = (T)(0.3 * (k + 1)); W(k, 1) = (T)(-0.2 * k + 0.1); }
+    Mat R = pca.GetReconstruction(W);
+    Mat F2 = pca.DimensionalityReductionFast(R);
+    EXPECT(MaxAbsDiff<T>(F2, W) <= tol * 50, std::string(tag) + " P2 basis^T basisInverse = I");
+    Mat Fall = pca.DimensionalityReduction(s.X, 3);
+    EXPECT(Fall.rows() == 3 && MaxAbsDiff<T>(Fall, Mat(F.topRows(3))) <= tol * 50, std::string(tag) + " P2 DimensionalityReduction(X, 3)");
+
+    const std::string prefix = std::string("/tmp/gprb200_pca_test_") + tag + "-";
+    pca.WriteMatricesToFile(prefix);
+    PCA<T> again(prefix, (int)r);
+    Mat R2 = again.GetReconstruction(W);
+    Mat F3 = again.DimensionalityReductionFast(s.X);
+    EXPECT(MaxAbsDiff<T>(R2, R) <= (sizeof(T) == 8 ? 0.0 : 1e-5), std::string(tag) + " P3 file round trip: reconstruction");
+    EXPECT(MaxAbsDiff<T>(F3, F) <= (sizeof(T) == 8 ? 1e-12 : 1e-3), std::string(tag) + " P3 file round trip: projection");
+    for (const char* f : {"Mean.bin", "Sigma.bin", "U.bin"}) std::remove((prefix + f).c_str());
+}
+
+void RunFused() {
+    typedef GaussianProcess<double> GP;
+    typedef GP::MatrixType Mat;
+    typedef GP::VectorType Vec;
+    const long D = 5000, n = 16, r = 5, N = 60;
+    Synth<double> s(D, n, r);
+    GP::Pointer gp(new GP(Kernel<double>::Pointer(new GaussianKernel<double>(1.7, 1.2))));
+    gp->SetSigma(0.1);
+    for (long i = 0; i < N; ++i) {
+        Vec x(2), y(r);
+        x[0] = std::sin(0.7 * i); x[1] = std::cos(0.3 * i);
+        for (long k = 0; k < r; ++k) y[k] = std::sin(x[0] * (k + 1)) + 0.5 * x[1];
+        gp->AddSample(x, y);
+    }
+    gp->Initialize();
+    PCA<double> pca(s.X, (int)r, gp);
+    const long T = 7;
+    Mat Xs(T, 2);
+    for (long t = 0; t < T; ++t) { Xs(t, 0) = 0.1 * t - 0.3; Xs(t, 1) = 0.9 - 0.05 * t; }
+    Mat W;
+    Mat fields = pca.PredictReconstruction(gp, Xs, &W);
+    double e = 0, ew = 0;
+    for (long t = 0; t < T; ++t) {
+        Vec x(2);
+        x[0] = Xs(t, 0); x[1] = Xs(t, 1);
+        Vec y = gp->Predict(x);
+        Mat w(r, 1);
+        for (long k = 0; k < r; ++k) { w(k, 0) = y[k]; ew = std::max(ew, std::fabs(y[k] - W(t, k))); }
+        Mat f = pca.GetReconstruction(w);
+        for (long i = 0; i < D; ++i) e = std::max(e, std::fabs(f(i, 0) - fields(i, t)));
+    }
+    EXPECT(ew <= 1e-13, "P4 fused weights == Predict");
+    EXPECT(e <= 1e-12, "P4 PredictReconstruction == GetReconstruction(Predict)");
+    bool threw = false;
+    try {
+        PCA<double> other(s.X, (int)r);
+        other.PredictReconstruction(gp, Xs);
+    } catch (std::string&) {
+        threw = true;
+    }
+    EXPECT(threw, "P4 a PCA on another handle is rejected");
+}
+
+int main() {
+    try {
+        RunAnalytic<double>("double", 1e-10);
+        RunAnalytic<float>("float", 2e-5);
+        RunFused();
+    } catch (std::string& s) {
+        std::cout << "[failed] exception: " << s << std::endl;
+        return 1;
+    }
+    std::cout << (failures ? "pca_device_test: FAILED" : "pca_device_test: all passed") << std::endl;
+    return failures ? 1 : 0;
+}

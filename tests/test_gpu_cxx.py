@@ -24,6 +24,14 @@ def test_cxx_device_program():
     assert rc == 0 and "[failed]" not in out, out[-4000:]
 
 
+def test_cxx_pca_program():
+    """PCA<T> (gpr_b200/cxx/include/PCA.h): analytic known answers, file round trip, fused Predict -> reconstruction."""
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "pca_device_test")
+    assert os.path.exists(exe), "tests/cxx/bin/pca_device_test missing: run __graft_entry__.build()"
+    rc, out = _run(exe)
+    assert rc == 0 and "[failed]" not in out, out[-4000:]
+
+
 DROPIN = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "dropin", "*")))
 
 
