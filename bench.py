@@ -34,6 +34,7 @@ C3_N, C3_D, C3_M, C3_SIGMA = 32768, 8, 1, 1.0
 C2_KERNEL = "GaussianKernel(8.215838362577491,1,)"  # sigma = 1.5 sqrt(30)
 C2_N, C2_D, C2_M, C2_SIGMA = 4096, 30, 786432, 1.0
 SEED = 0x6770725F62323030 % (2 ** 63)
+HBM_FALLBACK_GBS = 6650.0  # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 FP64_PEAK_TFLOPS = 37.1  # measured DMMA.8x8x4 issue rate on this pool's B200 (profiles/r01_fp64_probe.txt)
 FP64_CUBLAS_TFLOPS = 36.2  # measured cuBLAS DGEMM 16384^3 (profiles/r01_dgemm_ceiling.json)
 
@@ -278,6 +279,10 @@ def run_gpu(args):
     if rank == 0 and not args.skip_loglik:
         loglik = run_loglik(torch, gpr_b200, local_rank)
 
+    pca = None
+    if rank == 0 and not args.skip_pca:
+        pca = run_pca(torch, gpr_b200, local_rank)
+
     large = None
     if world > 1 and not args.skip_large:
         large = run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist)
@@ -329,6 +334,8 @@ def run_gpu(args):
             line["large_n"] = large
         if loglik:
             line["loglik"] = loglik
+        if pca:
+            line["pca_frame"] = pca
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
         if peaks:
@@ -467,6 +474,116 @@ def run_loglik(torch, gpr_b200, local_rank, N=16384, iters=3):
             "last_value": float(v[0]), "last_grad": [float(x) for x in g]}
 
 
+def run_pca(torch, gpr_b200, local_rank, D=3 * 64 ** 3, n=256, nF=32, N=256, d=30, frames=40):
+    """the per-frame path of gpPredict (apps/GaussianProcessPredict.cpp:188-203 +
+    include/DataParser.h:471-495): gp->Predict(v) -> principal weights -> PCA GetReconstruction -> the 3 x 64^3
+    displacement field, plus the training-time PCA fit (include/PCA.h:33-49) of n fields.
+    Device-resident frames are timed with CUDA events on the handle's stream; e2e frames go through the host-pointer
+    C-ABI (test point H2D, field D2H). Roofline: the reconstruct kernel streams 8 D nF bytes of basis per frame."""
+    from gpr_b200.pca import PCA
+    dev = torch.device("cuda", local_rank)
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 77)
+    rank_ = 48
+    grid = torch.linspace(0, 1, D, device=dev, dtype=torch.float64)
+    modes = torch.stack([torch.sin((k + 1) * np.pi * grid + 0.3 * k) for k in range(rank_)], dim=1)
+    amp = torch.logspace(0, -3, rank_, device=dev, dtype=torch.float64)
+    coef = torch.randn(rank_, n, generator=g, device=dev, dtype=torch.float64) * amp[:, None]
+    Xf = modes @ coef + 1e-4 * torch.randn(D, n, generator=g, device=dev, dtype=torch.float64) + 2.0
+    del modes
+    h = gpr_b200.Handle(local_rank)
+    stream = torch.cuda.current_stream(dev)
+    h.set_stream(stream.cuda_stream)
+    torch.cuda.synchronize()
+    p = PCA.fit_dev(Xf.data_ptr(), n, D, n, nF, h)          # warm-up fit (allocator, kernel attributes)
+    p.close()
+    l0 = h.launch_count()
+    p = PCA.fit_dev(Xf.data_ptr(), n, D, n, nF, h)
+    fit_ms, sweeps, fit_launches = p.stat("fit_ms"), p.stat("sweeps"), h.launch_count() - l0
+    sigma = p.GetEigenvalues()
+    # the GP that predicts the principal weights: inputs = d surrogate features, outputs = the training fields' weights
+    F = torch.empty(nF, n, device=dev, dtype=torch.float64)
+    p.project_dev(Xf.data_ptr(), n, n, nF, F.data_ptr(), n)
+    rng = np.random.default_rng(SEED + 78)
+    Xin = rng.standard_normal((N, d))
+    Y = F.T.contiguous().cpu().numpy()[:N]
+    ops, params = gpr_b200.KernelFactory.GetKernel("GaussianKernel(8,1,)").lower()
+    h.set_kernel(ops, params)
+    h.set_train(Xin, Y, 0.1)
+    h.learn(0)
+    Xs = torch.from_numpy(rng.standard_normal((frames, d))).to(dev)
+    out = torch.empty(D, device=dev, dtype=torch.float64)
+    W = torch.empty(frames, 32, device=dev, dtype=torch.float64)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for t in range(3):
+        p.predict_reconstruct_dev(h, Xs[t].data_ptr(), 1, out.data_ptr(), 1)
+    l0 = h.launch_count()
+    e0.record(stream)
+    for t in range(frames):
+        p.predict_reconstruct_dev(h, Xs[t].data_ptr(), 1, out.data_ptr(), 1)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    frame_ms = e0.elapsed_time(e1) / frames
+    frame_launches = (h.launch_count() - l0) / frames
+    # the reconstruct kernel alone (the HBM stream): weights already on the device
+    h.predict_dev(Xs.data_ptr(), frames, W.data_ptr(), 32)
+    for t in range(3):
+        p.reconstruct_dev(W[t].data_ptr(), 32, 1, 1, out.data_ptr(), 1)
+    e0.record(stream)
+    for t in range(frames):
+        p.reconstruct_dev(W[t].data_ptr(), 32, 1, 1, out.data_ptr(), 1)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    rec_ms = e0.elapsed_time(e1) / frames
+    rec_bytes = 8.0 * D * nF + 8.0 * D + 8.0 * D
+    # DimensionalityReductionFast of one field (the input side of the frame, include/DataParser.h:225-229)
+    Fo = torch.empty(nF, device=dev, dtype=torch.float64)
+    col = Xf[:, 0].contiguous()
+    for t in range(3):
+        p.project_dev(col.data_ptr(), 1, 1, nF, Fo.data_ptr(), 1)
+    e0.record(stream)
+    for t in range(frames):
+        p.project_dev(col.data_ptr(), 1, 1, nF, Fo.data_ptr(), 1)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    proj_ms = e0.elapsed_time(e1) / frames
+    proj_bytes = 8.0 * D * nF + 8.0 * D + 8.0 * D
+    # end to end: host test point in, host field out
+    Xs_h = Xs.cpu().pin_memory()
+    fields = torch.empty(D, dtype=torch.float64).pin_memory()
+    for t in range(2):
+        h._ck(h.lib.gprb200_predict_reconstruct(h.h, p.p, Xs_h[t].data_ptr(), 1, fields.data_ptr(), None))
+    t0 = time.perf_counter()
+    for t in range(frames):
+        h._ck(h.lib.gprb200_predict_reconstruct(h.h, p.p, Xs_h[t].data_ptr(), 1, fields.data_ptr(), None))
+    e2e_ms = (time.perf_counter() - t0) / frames * 1e3
+    # parity property at full size: reconstruct(project(x)) reproduces a training field up to the discarded modes
+    back = torch.empty(D, 4, device=dev, dtype=torch.float64)
+    p.reconstruct_dev(F.data_ptr(), n, 0, 4, back.data_ptr(), 4)
+    tail = float(np.sqrt(np.sum(sigma[nF:] ** 2)) / np.sqrt(np.sum(sigma ** 2)))
+    rt = float((back - Xf[:, :4]).norm() / (Xf[:, :4] - Xf.mean(dim=1, keepdim=True)).norm())
+    peaks = measured_peaks()
+    hbm = peaks.get("hbm_gbs", HBM_FALLBACK_GBS) if peaks else HBM_FALLBACK_GBS
+    ach = rec_bytes / (rec_ms * 1e-3) * 1e-9
+    p.close()
+    h.close()
+    del Xf
+    torch.cuda.empty_cache()
+    return {"metric": "frames_per_s", "value": 1e3 / frame_ms, "unit": "frames/s",
+            "config": {"workload": "gpPredict frame: Predict (N=%d, d=%d, M=%d) -> PCA GetReconstruction (D=%d)" % (N, d, nF, D),
+                       "D": D, "n_train_fields": n, "nFeatures": nF},
+            "ms_per_frame": frame_ms, "launches_per_frame": frame_launches,
+            "e2e": {"value": 1e3 / e2e_ms, "unit": "frames/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": 8 * d,
+                    "d2h_bytes_per_step": 8 * D},
+            "roofline": {"kernel": "pca_reconstruct_kernel<1>", "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s",
+                         "frac": ach / hbm, "traffic": None, "ms": rec_ms, "algorithmic_bytes": rec_bytes},
+            "project": {"kernel": "pca_project_kernel<1>", "ms": proj_ms, "achieved_gbs": proj_bytes / (proj_ms * 1e-3) * 1e-9,
+                        "frac": proj_bytes / (proj_ms * 1e-3) * 1e-9 / hbm, "algorithmic_bytes": proj_bytes},
+            "fit": {"ms": fit_ms, "jacobi_sweeps": sweeps, "launches": fit_launches,
+                    "note": "mean + 2 x (split-K DMMA Gram, parallel Jacobi, Z <- Z V) on D x n = %d x %d" % (D, n)},
+            "round_trip_rel_err": rt, "discarded_energy": tail}
+
+
 def run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist):
     """C5: ONE model of N = 131072 samples factored across all ranks (block-cyclic Cholesky, NCCL panel broadcasts,
     gpr_b200/dist.py) + distributed solve. Strong scaling of a single large problem; device-timed, max over ranks."""
@@ -555,6 +672,7 @@ def main():
     ap.add_argument("--skip-predict", action="store_true")
     ap.add_argument("--skip-large", action="store_true")
     ap.add_argument("--skip-loglik", action="store_true")
+    ap.add_argument("--skip-pca", action="store_true")
     ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")

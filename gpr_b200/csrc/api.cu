@@ -262,7 +262,13 @@ int predict_impl(Ctx* c, const double* dXs, int64_t T, double* d_mean, int64_t l
     GP_TRY(require(c, c->have_train, "predict: gaussian process is not initialized"));
     if (!c->have_alpha) GP_TRY(ensure_alpha(c));
     const int64_t N = c->N, M = c->M;
-    PhaseTimer t(c, GPRB200_T_PREDICT);
+    // Predict stays asynchronous (a per-frame call must not cost a host synchronisation): the phase time is taken
+    // with two persistent events and resolved only when gprb200_phase_ms asks for it.
+    if (!c->ev0) {
+        GP_CUDA(c, cudaEventCreate(&c->ev0));
+        GP_CUDA(c, cudaEventCreate(&c->ev1));
+    }
+    GP_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     if (d_mean) {
         const int64_t ldkx = round_up(N, 16);
         TempBuf Kx(c);
@@ -298,8 +304,8 @@ int predict_impl(Ctx* c, const double* dXs, int64_t T, double* d_mean, int64_t l
         ++c->launches;
         GP_CUDA(c, cudaGetLastError());
     }
-    t.stop();
-    t.resolve();
+    GP_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->predict_time_pending = true;
     return 0;
 }
 
@@ -368,6 +374,8 @@ int gprb200_destroy(gprb200_handle h) {
     free_model(c);
     cudaFree(c->dInfo);
     cudaFree(c->dScratch);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     if (c->panel_stream) cudaStreamDestroy(c->panel_stream);
     delete c;
@@ -397,6 +405,12 @@ int64_t gprb200_launch_count(gprb200_handle h) { return h ? h->launches : -1; }
 
 int gprb200_phase_ms(gprb200_handle h, double* ms) {
     if (!h || !ms) return -2;
+    if (h->predict_time_pending && h->ev1) {
+        float t = 0.f;
+        if (cudaEventSynchronize(h->ev1) == cudaSuccess && cudaEventElapsedTime(&t, h->ev0, h->ev1) == cudaSuccess)
+            h->phase_ms[GPRB200_T_PREDICT] = t;
+        h->predict_time_pending = false;
+    }
     for (int i = 0; i < GPRB200_T_COUNT; ++i) ms[i] = h->phase_ms[i];
     return 0;
 }

@@ -80,7 +80,8 @@ struct Ctx {
     double prof_tb_ms = 0.0, prof_tb_flops = 0.0, prof_tb_launches = 0.0;  // last factorisation
     double prof_gemv_ms = 0.0, prof_gemv_bytes = 0.0, prof_gemv_launches = 0.0;  // accumulated since reset
 
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // Predict phase timing (resolved lazily by gprb200_phase_ms)
+    bool predict_time_pending = false;
     double phase_ms[GPRB200_T_COUNT] = {0};
 };
 

@@ -102,11 +102,8 @@ __device__ __forceinline__ void jacobi_pair(int s, int t, int n2, int& p, int& q
     q = max(a, b);
 }
 
-__global__ void pca_jacobi_rot_kernel(const double* __restrict__ A, int n2, int n, int step, double2* __restrict__ cs) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n2 / 2) return;
-    int p, q;
-    jacobi_pair(step, t, n2, p, q);
+// rotation that annihilates A[p][q]: A <- J^T A J with J = [[c, s], [-s, c]] in the (p, q) plane
+__device__ __forceinline__ double2 jacobi_rotation(const double* __restrict__ A, int n2, int n, int p, int q) {
     double c = 1.0, s = 0.0;
     if (q < n) {
         const double apq = A[(int64_t)p * n2 + q], app = A[(int64_t)p * n2 + p], aqq = A[(int64_t)q * n2 + q];
@@ -117,11 +114,13 @@ __global__ void pca_jacobi_rot_kernel(const double* __restrict__ A, int n2, int 
             s = tt * c;
         }
     }
-    cs[t] = make_double2(c, s);
+    return make_double2(c, s);
 }
 
-__global__ void __launch_bounds__(PT) pca_jacobi_apply_kernel(double* __restrict__ A, double* __restrict__ V, int n2,
-                                                              int step, const double2* __restrict__ cs) {
+// One round-robin step in ONE launch: every thread derives the two rotations it needs from the previous matrix Ain
+// (read-only during the launch) and writes its 2 x 2 block of Aout; V is rotated in place (its threads read Ain only).
+__global__ void __launch_bounds__(PT) pca_jacobi_step_kernel(const double* __restrict__ Ain, double* __restrict__ Aout,
+                                                             double* __restrict__ V, int n2, int n, int step) {
     const int m = n2 / 2;
     const int64_t e = (int64_t)blockIdx.x * PT + threadIdx.x;
     const int64_t nA = (int64_t)m * m;
@@ -130,26 +129,28 @@ __global__ void __launch_bounds__(PT) pca_jacobi_apply_kernel(double* __restrict
         int pa, qa, pb, qb;
         jacobi_pair(step, ta, n2, pa, qa);
         jacobi_pair(step, tb, n2, pb, qb);
-        const double2 ra = cs[ta], rb = cs[tb];
-        if (ra.y == 0.0 && rb.y == 0.0) return;
-        double* a0 = A + (int64_t)pa * n2;
-        double* a1 = A + (int64_t)qa * n2;
+        const double2 ra = jacobi_rotation(Ain, n2, n, pa, qa);
+        const double2 rb = (ta == tb) ? ra : jacobi_rotation(Ain, n2, n, pb, qb);
+        const double* a0 = Ain + (int64_t)pa * n2;
+        const double* a1 = Ain + (int64_t)qa * n2;
         const double b00 = a0[pb], b01 = a0[qb], b10 = a1[pb], b11 = a1[qb];
         const double n00 = rb.x * b00 - rb.y * b01, n01 = rb.y * b00 + rb.x * b01;
         const double n10 = rb.x * b10 - rb.y * b11, n11 = rb.y * b10 + rb.x * b11;
         double r00 = ra.x * n00 - ra.y * n10, r10 = ra.y * n00 + ra.x * n10;
         double r01 = ra.x * n01 - ra.y * n11, r11 = ra.y * n01 + ra.x * n11;
-        if (ta == tb) r01 = r10 = 0.0;  // the annihilated pair
-        a0[pb] = r00; a0[qb] = r01; a1[pb] = r10; a1[qb] = r11;
+        if (ta == tb && ra.y != 0.0) r01 = r10 = 0.0;  // the annihilated pair
+        double* o0 = Aout + (int64_t)pa * n2;
+        double* o1 = Aout + (int64_t)qa * n2;
+        o0[pb] = r00; o0[qb] = r01; o1[pb] = r10; o1[qb] = r11;
         return;
     }
     const int64_t f = e - nA;
     if (f >= (int64_t)n2 * m) return;
     const int i = (int)(f / m), tb = (int)(f % m);
-    const double2 rb = cs[tb];
-    if (rb.y == 0.0) return;
     int pb, qb;
     jacobi_pair(step, tb, n2, pb, qb);
+    const double2 rb = jacobi_rotation(Ain, n2, n, pb, qb);
+    if (rb.y == 0.0) return;
     double* v = V + (int64_t)i * n2;
     const double vp = v[pb], vq = v[qb];
     v[pb] = rb.x * vp - rb.y * vq;
@@ -209,102 +210,170 @@ __global__ void pca_pack_kernel(const double* __restrict__ U, int64_t ldu, const
 }
 
 // ---- project: F[k][t] = scale_k * sum_i B[i][k] (X[i][t] - mean[i]) ------------------------------------------
-// grid (ceil(K / 32), splits): lane = mode k (a row of B is read as one coalesced run), warps stride the rows of
-// this CTA's slab; partial[split][k][t], combined in a fixed order by pca_project_reduce_kernel.
+// grid (ceil(K / 32), splits): HBM stream over B (8 D K bytes). A group of 16 lanes reads one row's 32 modes with
+// one 16-byte load per lane, PU rows per group in flight; every lane keeps two mode sums per column.
+// partial[split][k][t], combined in a fixed order by pca_project_reduce_kernel.
 template <int NC>
 __global__ void __launch_bounds__(PT) pca_project_kernel(const double* __restrict__ B, int64_t ldb, int K,
                                                          const double* __restrict__ X, int64_t ldx, int T,
                                                          const double* __restrict__ mean, int64_t D, int64_t rows_per_split,
                                                          double* __restrict__ partial) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int k = blockIdx.x * 32 + lane;
+    constexpr int PU = (NC == 1) ? 8 : 4;  // rows in flight per group
+    const int tid = threadIdx.x, sub = tid & 15, grp = tid >> 4;
+    const int k = blockIdx.x * 32 + 2 * sub;
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_split;
     const int64_t r1 = min(D, r0 + rows_per_split);
-    double acc[NC];
+    double acc[2][NC];
 #pragma unroll
-    for (int t = 0; t < NC; ++t) acc[t] = 0.0;
-    const bool live = k < K;
-#pragma unroll 4
-    for (int64_t i = r0 + warp; i < r1; i += PT / 32) {
-        const double b = live ? B[i * ldb + k] : 0.0;
-        const double mu = mean[i];
-        const double* x = X + i * ldx;
+    for (int t = 0; t < NC; ++t) acc[0][t] = acc[1][t] = 0.0;
+    const bool live0 = k < K, live1 = k + 1 < K;
+    for (int64_t i0 = r0 + grp * PU; i0 < r1; i0 += (PT / 16) * PU) {
+        double2 b[PU];
+        double xc[PU][NC];
 #pragma unroll
-        for (int t = 0; t < NC; ++t)
-            if (t < T) acc[t] = fma(b, x[t] - mu, acc[t]);
+        for (int u = 0; u < PU; ++u) {
+            const int64_t i = i0 + u;
+            b[u] = make_double2(0.0, 0.0);
+            if (i < r1) {
+                const double* src = B + i * ldb + k;  // ldb even, k even: 16-byte aligned
+                if (live1) b[u] = __ldcs(reinterpret_cast<const double2*>(src));
+                else if (live0) b[u].x = __ldcs(src);
+                const double mu = mean[i];
+#pragma unroll
+                for (int t = 0; t < NC; ++t) xc[u][t] = (t < T) ? X[i * ldx + t] - mu : 0.0;
+            } else {
+#pragma unroll
+                for (int t = 0; t < NC; ++t) xc[u][t] = 0.0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < PU; ++u)
+#pragma unroll
+            for (int t = 0; t < NC; ++t) {
+                acc[0][t] = fma(b[u].x, xc[u][t], acc[0][t]);
+                acc[1][t] = fma(b[u].y, xc[u][t], acc[1][t]);
+            }
     }
-    __shared__ double red[PT / 32][32][NC];
+    __shared__ double red[PT / 16][32][NC];
 #pragma unroll
-    for (int t = 0; t < NC; ++t) red[warp][lane][t] = acc[t];
+    for (int t = 0; t < NC; ++t) {
+        red[grp][2 * sub][t] = acc[0][t];
+        red[grp][2 * sub + 1][t] = acc[1][t];
+    }
     __syncthreads();
-    if (warp == 0 && live) {
+    if (tid < 32 && blockIdx.x * 32 + tid < K) {
 #pragma unroll
         for (int t = 0; t < NC; ++t) {
             double s = 0.0;
 #pragma unroll
-            for (int w = 0; w < PT / 32; ++w) s += red[w][lane][t];
-            partial[((int64_t)blockIdx.y * K + k) * NC + t] = s;
+            for (int g = 0; g < PT / 16; ++g) s += red[g][tid][t];
+            partial[((int64_t)blockIdx.y * K + blockIdx.x * 32 + tid) * NC + t] = s;
         }
     }
 }
 
+// one warp per mode k: lanes stride the splits, fixed-order shuffle tree (deterministic)
 template <int NC>
-__global__ void pca_project_reduce_kernel(const double* __restrict__ partial, int splits, int K, int T,
-                                          const double* __restrict__ sigma, double null_below, double* __restrict__ F,
-                                          int64_t ldf) {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= K * NC) return;
-    const int k = e / NC, t = e % NC;
-    if (t >= T) return;
-    double s = 0.0;
-    for (int z = 0; z < splits; ++z) s += partial[((int64_t)z * K + k) * NC + t];
-    if (sigma) s = (sigma[k] > null_below) ? s / sigma[k] : 0.0;
-    F[(int64_t)k * ldf + t] = s;
+__global__ void __launch_bounds__(256) pca_project_reduce_kernel(const double* __restrict__ partial, int splits, int K, int T,
+                                                                 const double* __restrict__ sigma, double null_below,
+                                                                 double* __restrict__ F, int64_t ldf) {
+    const int lane = threadIdx.x & 31;
+    const int k = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (k >= K) return;
+    double s[NC];
+#pragma unroll
+    for (int t = 0; t < NC; ++t) s[t] = 0.0;
+    for (int z = lane; z < splits; z += 32) {
+        const double* p = partial + ((int64_t)z * K + k) * NC;
+#pragma unroll
+        for (int t = 0; t < NC; ++t) s[t] += p[t];
+    }
+#pragma unroll
+    for (int t = 0; t < NC; ++t) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s[t] += __shfl_xor_sync(0xffffffffu, s[t], o);
+        if (lane == 0 && t < T) {
+            double v = s[t];
+            if (sigma) v = (sigma[k] > null_below) ? v / sigma[k] : 0.0;
+            F[(int64_t)k * ldf + t] = v;
+        }
+    }
 }
 
 // ---- reconstruct: out[i][t] = mean[i] + sum_k Binv[i][k] w(k, t) ------------------------------------------------
-// CTA = 128 rows; a 128 x 32 slab of Binv is staged through shared memory with coalesced loads, thread r then owns
-// row r. w(k, t) = W[k*ldw + t], or W[t*ldw + k] when the weights come straight out of Predict (T x M row-major).
-constexpr int RR = 128, RK = 32;
+// HBM stream over Binv (8 D nF bytes). A group of 16 lanes owns a row: one 16-byte load per lane covers 32 modes,
+// RU rows per group are in flight at once, the dot products are folded with 4 shuffle steps. The weights sit in
+// shared memory. w(k, t) = W[k*ldw + t], or W[t*ldw + k] when they come straight out of Predict (T x M row-major).
+constexpr int RT = 256;   // threads per CTA = 16 row groups
+constexpr int RU = 4;     // rows in flight per group
+constexpr int RROWS = (RT / 16) * RU;
+constexpr int RMAXF = 512;  // modes held in shared memory per pass
 template <int NC>
-__global__ void __launch_bounds__(RR) pca_reconstruct_kernel(const double* __restrict__ Binv, int64_t ldb, int nF,
+__global__ void __launch_bounds__(RT) pca_reconstruct_kernel(const double* __restrict__ Binv, int64_t ldb, int nF,
                                                              const double* __restrict__ W, int64_t ldw, int w_transposed,
                                                              int T, const double* __restrict__ mean, int64_t D,
                                                              double* __restrict__ out, int64_t ldo) {
-    __shared__ double tile[RR][RK + 1];
-    __shared__ double sw[RK][NC];
-    const int tid = threadIdx.x;
-    const int64_t row0 = (int64_t)blockIdx.x * RR;
-    const int64_t row = row0 + tid;
-    double acc[NC];
+    __shared__ double sw[NC][RMAXF];
+    const int tid = threadIdx.x, sub = tid & 15, grp = tid >> 4;
+    const int64_t row0 = (int64_t)blockIdx.x * RROWS + grp * RU;
+    double acc[RU][NC];
 #pragma unroll
-    for (int t = 0; t < NC; ++t) acc[t] = 0.0;
-    for (int k0 = 0; k0 < nF; k0 += RK) {
-        const int kn = min(RK, nF - k0);
+    for (int u = 0; u < RU; ++u)
+#pragma unroll
+        for (int t = 0; t < NC; ++t) acc[u][t] = 0.0;
+    for (int f0 = 0; f0 < nF; f0 += RMAXF) {
+        const int fn = min(RMAXF, nF - f0);
         __syncthreads();
-        for (int e = tid; e < RR * RK; e += RR) {
-            const int r = e / RK, kk = e % RK;
-            tile[r][kk] = (kk < kn && row0 + r < D) ? Binv[(row0 + r) * ldb + k0 + kk] : 0.0;
-        }
-        for (int e = tid; e < RK * NC; e += RR) {
-            const int kk = e / NC, t = e % NC;
+        for (int e = tid; e < NC * RMAXF; e += RT) {
+            const int t = e / RMAXF, k = e % RMAXF;
             double v = 0.0;
-            if (kk < kn && t < T) v = w_transposed ? W[(int64_t)t * ldw + k0 + kk] : W[(int64_t)(k0 + kk) * ldw + t];
-            sw[kk][t] = v;
+            if (k < fn && t < T) v = w_transposed ? W[(int64_t)t * ldw + f0 + k] : W[(int64_t)(f0 + k) * ldw + t];
+            sw[t][k] = v;
         }
         __syncthreads();
-#pragma unroll 8
-        for (int kk = 0; kk < RK; ++kk) {
-            const double b = tile[tid][kk];
+        for (int k0 = 0; k0 < fn; k0 += 32) {
+            const int k = k0 + 2 * sub;  // ldb is even and Binv 16-byte aligned: (row, k) starts a double2
+            double2 b[RU];
 #pragma unroll
-            for (int t = 0; t < NC; ++t) acc[t] = fma(b, sw[kk][t], acc[t]);
+            for (int u = 0; u < RU; ++u) {
+                b[u] = make_double2(0.0, 0.0);
+                if (row0 + u < D && k < fn) {
+                    const double* src = Binv + (row0 + u) * ldb + f0 + k;
+                    if (k + 1 < fn) b[u] = __ldcs(reinterpret_cast<const double2*>(src));
+                    else b[u].x = __ldcs(src);
+                }
+            }
+            const int kc = min(k, RMAXF - 2);
+#pragma unroll
+            for (int t = 0; t < NC; ++t) {
+                const double w0 = sw[t][kc], w1 = sw[t][kc + 1];
+#pragma unroll
+                for (int u = 0; u < RU; ++u) acc[u][t] = fma(b[u].y, w1, fma(b[u].x, w0, acc[u][t]));
+            }
         }
     }
-    if (row < D) {
-        const double mu = mean[row];
 #pragma unroll
-        for (int t = 0; t < NC; ++t)
-            if (t < T) out[row * ldo + t] = mu + acc[t];
+    for (int u = 0; u < RU; ++u)
+#pragma unroll
+        for (int t = 0; t < NC; ++t) {
+            double v = acc[u][t];
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            acc[u][t] = v;
+        }
+    if (sub < RU) {  // lane u of the group writes row u (consecutive rows -> adjacent addresses)
+        const int64_t row = row0 + sub;
+        if (row < D) {
+            const double mu = mean[row];
+#pragma unroll
+            for (int t = 0; t < NC; ++t) {
+                double v = 0.0;
+#pragma unroll
+                for (int u = 0; u < RU; ++u)
+                    if (u == sub) v = acc[u][t];
+                if (t < T) out[row * ldo + t] = mu + v;
+            }
+        }
     }
 }
 
@@ -313,7 +382,7 @@ int project_chunk(PcaModel* m, const double* B, int64_t ldb, int K, const double
                   const double* dX, int64_t ldx, int T, double* dF, int64_t ldf) {
     Ctx* c = m->c;
     const int kblocks = (K + 31) / 32;
-    int64_t splits = std::max<int64_t>(1, (148 * 4 + kblocks - 1) / kblocks);
+    int64_t splits = std::max<int64_t>(1, (148 * 6 + kblocks - 1) / kblocks);
     splits = std::min<int64_t>(splits, std::max<int64_t>(1, m->D / 256));
     const int64_t rps = (m->D + splits - 1) / splits;
     splits = (m->D + rps - 1) / rps;
@@ -321,7 +390,7 @@ int project_chunk(PcaModel* m, const double* B, int64_t ldb, int K, const double
     GP_CUDA(c, cudaMallocAsync((void**)&partial, sizeof(double) * splits * K * NC, c->stream));
     pca_project_kernel<NC><<<dim3((unsigned)kblocks, (unsigned)splits), PT, 0, c->stream>>>(B, ldb, K, dX, ldx, T, m->dMean,
                                                                                            m->D, rps, partial);
-    pca_project_reduce_kernel<NC><<<(K * NC + 255) / 256, 256, 0, c->stream>>>(partial, (int)splits, K, T, sigma, null_below,
+    pca_project_reduce_kernel<NC><<<(K + 7) / 8, 256, 0, c->stream>>>(partial, (int)splits, K, T, sigma, null_below,
                                                                               dF, ldf);
     c->launches += 2;
     GP_CUDA(c, cudaGetLastError());
@@ -354,19 +423,19 @@ int reconstruct_dev(PcaModel* m, const double* dW, int64_t ldw, int transposed, 
     Ctx* c = m->c;
     if (!m->dBinv) return fail(c, -2, "PCA: no basis (fit or set first)");
     if (nrows_w != m->nF) return fail(c, -2, "PCA::GetReconstruction: weights must have nFeatures rows");
-    const unsigned blocks = (unsigned)((m->D + RR - 1) / RR);
+    const unsigned blocks = (unsigned)((m->D + RROWS - 1) / RROWS);
     for (int64_t t0 = 0; t0 < T; t0 += 8) {
         const int tn = (int)std::min<int64_t>(8, T - t0);
         const double* w = transposed ? dW + t0 * ldw : dW + t0;
         double* o = dOut + t0;
         if (tn <= 1)
-            pca_reconstruct_kernel<1><<<blocks, RR, 0, c->stream>>>(m->dBinv, m->ldb, (int)m->nF, w, ldw, transposed, tn,
+            pca_reconstruct_kernel<1><<<blocks, RT, 0, c->stream>>>(m->dBinv, m->ldb, (int)m->nF, w, ldw, transposed, tn,
                                                                    m->dMean, m->D, o, ldo);
         else if (tn <= 4)
-            pca_reconstruct_kernel<4><<<blocks, RR, 0, c->stream>>>(m->dBinv, m->ldb, (int)m->nF, w, ldw, transposed, tn,
+            pca_reconstruct_kernel<4><<<blocks, RT, 0, c->stream>>>(m->dBinv, m->ldb, (int)m->nF, w, ldw, transposed, tn,
                                                                    m->dMean, m->D, o, ldo);
         else
-            pca_reconstruct_kernel<8><<<blocks, RR, 0, c->stream>>>(m->dBinv, m->ldb, (int)m->nF, w, ldw, transposed, tn,
+            pca_reconstruct_kernel<8><<<blocks, RT, 0, c->stream>>>(m->dBinv, m->ldb, (int)m->nF, w, ldw, transposed, tn,
                                                                    m->dMean, m->D, o, ldo);
         ++c->launches;
         GP_CUDA(c, cudaGetLastError());
@@ -391,8 +460,10 @@ int pack_basis(PcaModel* m) {
 }
 
 // ---- fit ---------------------------------------------------------------------------------------------------------
-// Jacobi eigen-decomposition of the n2 x n2 matrix in dA (destroyed; diagonal = eigenvalues), dV = eigenvectors.
-int jacobi_eig(PcaModel* m, double* dA, double* dV, int n2, int n, double2* dCs, double* dNorm, int* sweeps_out) {
+// Jacobi eigen-decomposition of the n2 x n2 matrix in dA (destroyed), dB = same-size work matrix (the steps
+// ping-pong between the two); on return *dRes points at the one whose diagonal holds the eigenvalues, dV = vectors.
+int jacobi_eig(PcaModel* m, double* dA, double* dB, double* dV, int n2, int n, double* dNorm, int* sweeps_out,
+               double** dRes) {
     Ctx* c = m->c;
     GP_TRY(set_identity(c, dV, n2, n2));
     const int half = n2 / 2;
@@ -401,13 +472,14 @@ int jacobi_eig(PcaModel* m, double* dA, double* dV, int n2, int n, double2* dCs,
     const double tol = (double)n2 * 1e-16;
     bool converged = false;
     int sweep = 0;
+    double *cur = dA, *nxt = dB;
     for (; sweep < 40; ++sweep) {
         for (int step = 0; step < n2 - 1; ++step) {
-            pca_jacobi_rot_kernel<<<(half + 127) / 128, 128, 0, c->stream>>>(dA, n2, n, step, dCs);
-            pca_jacobi_apply_kernel<<<ablocks, PT, 0, c->stream>>>(dA, dV, n2, step, dCs);
+            pca_jacobi_step_kernel<<<ablocks, PT, 0, c->stream>>>(cur, nxt, dV, n2, n, step);
+            std::swap(cur, nxt);
         }
-        c->launches += 2 * (int64_t)(n2 - 1);
-        pca_offnorm_kernel<<<1, 1024, 0, c->stream>>>(dA, n2, dNorm);
+        c->launches += (int64_t)(n2 - 1);
+        pca_offnorm_kernel<<<1, 1024, 0, c->stream>>>(cur, n2, dNorm);
         ++c->launches;
         GP_CUDA(c, cudaGetLastError());
         double nrm[2];
@@ -419,6 +491,7 @@ int jacobi_eig(PcaModel* m, double* dA, double* dV, int n2, int n, double2* dCs,
         if (nrm[0] == 0.0) { ++sweep; break; }
     }
     *sweeps_out = sweep;
+    *dRes = cur;
     return 0;
 }
 
@@ -448,19 +521,18 @@ int fit_dev(PcaModel* m, const double* dX, int64_t ldx, int64_t D, int64_t n, in
     GP_TRY(pca_alloc(c, &m->dMean, (size_t)D));
     GP_TRY(pca_alloc(c, &m->dSigma, (size_t)n));
     GP_TRY(pca_alloc(c, &m->dU, (size_t)Dpad * m->ldu));
-    double *dZt = nullptr, *dPart = nullptr, *dA = nullptr, *dV = nullptr, *dW = nullptr, *dNorm = nullptr, *dScale = nullptr;
-    double2* dCs = nullptr;
+    double *dZt = nullptr, *dPart = nullptr, *dA = nullptr, *dB = nullptr, *dV = nullptr, *dW = nullptr, *dNorm = nullptr, *dScale = nullptr;
     int* dPerm = nullptr;
     int rc = 0;
     auto body = [&]() -> int {
         GP_TRY(pca_alloc(c, &dZt, (size_t)Dpad * m->ldu));
         GP_TRY(pca_alloc(c, &dPart, (size_t)batch * n * ldg));
         GP_TRY(pca_alloc(c, &dA, (size_t)n2 * n2));
+        GP_TRY(pca_alloc(c, &dB, (size_t)n2 * n2));
         GP_TRY(pca_alloc(c, &dV, (size_t)n2 * n2));
         GP_TRY(pca_alloc(c, &dW, (size_t)n * ldg));
         GP_TRY(pca_alloc(c, &dNorm, 2));
         GP_TRY(pca_alloc(c, &dScale, (size_t)n));
-        GP_TRY(pca_alloc(c, &dCs, (size_t)n2 / 2));
         GP_TRY(pca_alloc(c, &dPerm, (size_t)n));
         const int passes = std::max(1, m->passes);
         double* zin = (passes % 2 == 0) ? m->dU : dZt;  // ping-pong so that the last product lands in dU
@@ -486,9 +558,10 @@ int fit_dev(PcaModel* m, const double* dX, int64_t ldx, int64_t D, int64_t n, in
             ++c->launches;
             GP_CUDA(c, cudaGetLastError());
             int sw = 0;
-            GP_TRY(jacobi_eig(m, dA, dV, n2, (int)n, dCs, dNorm, &sw));
+            double* dEig = nullptr;
+            GP_TRY(jacobi_eig(m, dA, dB, dV, n2, (int)n, dNorm, &sw, &dEig));
             m->sweeps += sw;
-            pca_diag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(dA, n2, (int)n, dScale);
+            pca_diag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(dEig, n2, (int)n, dScale);
             ++c->launches;
             GP_CUDA(c, cudaMemcpyAsync(lam.data(), dScale, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
             GP_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -519,8 +592,8 @@ int fit_dev(PcaModel* m, const double* dX, int64_t ldx, int64_t D, int64_t n, in
     };
     rc = body();
     cudaStreamSynchronize(c->stream);
-    cudaFree(dZt); cudaFree(dPart); cudaFree(dA); cudaFree(dV); cudaFree(dW); cudaFree(dNorm); cudaFree(dScale);
-    cudaFree(dCs); cudaFree(dPerm);
+    cudaFree(dZt); cudaFree(dPart); cudaFree(dA); cudaFree(dB); cudaFree(dV); cudaFree(dW); cudaFree(dNorm); cudaFree(dScale);
+    cudaFree(dPerm);
     if (rc == 0) {
         cudaEventRecord(e1, c->stream);
         cudaEventSynchronize(e1);

@@ -52,6 +52,34 @@ class PCA:
         self.D, self.n = U.shape
         return self
 
+    @classmethod
+    def fit_dev(cls, dX_ptr, ldx, D, n, nFeatures, handle, passes=None):
+        """Fit from a D x n matrix already in HBM (device pointer, leading dimension ldx)."""
+        self = cls.__new__(cls)
+        self._own = False
+        self.handle = handle
+        self.lib = handle.lib
+        self.p = C.c_void_p()
+        self._ck(self.lib.gprb200_pca_create(handle.h, C.byref(self.p)))
+        self.nFeatures = int(nFeatures)
+        if passes is not None:
+            self._ck(self.lib.gprb200_pca_set_option(self.p, b"passes", int(passes)))
+        self._ck(self.lib.gprb200_pca_fit_dev(self.p, C.c_void_p(dX_ptr), ldx, D, n, self.nFeatures))
+        self.D, self.n = int(D), int(n)
+        return self
+
+    def reconstruct_dev(self, dW_ptr, ldw, transposed, T, dOut_ptr, ldo):
+        self._ck(self.lib.gprb200_pca_reconstruct_dev(self.p, C.c_void_p(dW_ptr), ldw, int(transposed), self.nFeatures, T,
+                                                      C.c_void_p(dOut_ptr), ldo))
+
+    def project_dev(self, dX_ptr, ldx, T, rows_out, dF_ptr, ldf):
+        self._ck(self.lib.gprb200_pca_project_dev(self.p, C.c_void_p(dX_ptr), ldx, T, rows_out, C.c_void_p(dF_ptr), ldf))
+
+    def predict_reconstruct_dev(self, gp_handle, dXs_ptr, T, dFields_ptr, ldo, dW_ptr=None, ldw=0):
+        self._ck(self.lib.gprb200_predict_reconstruct_dev(gp_handle.h, self.p, C.c_void_p(dXs_ptr), T,
+                                                          C.c_void_p(dFields_ptr), ldo,
+                                                          C.c_void_p(dW_ptr) if dW_ptr else None, ldw))
+
     def _ck(self, rc):
         if rc != 0:
             raise GprError(rc, self.lib.gprb200_last_error(self.handle.h).decode())
