@@ -14,3 +14,5 @@ from .kernels import (  # noqa: E402,F401
 from .gp import (  # noqa: E402,F401
     GaussianProcess, GaussianLogLikelihood, GaussianLikelihood, ReadMatrix, WriteMatrix,
     FullPivotLU, JacobiSVD, BDCSVD, SelfAdjointEigenSolver)
+from .inference import GaussianProcessInference  # noqa: E402,F401
+from .pca import PCA  # noqa: E402,F401

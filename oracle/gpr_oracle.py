@@ -334,3 +334,74 @@ class PCAOracle:
         (i, i), which reads out of bounds for i >= 1 in a column vector; not reproduced."""
         c = np.cumsum(self.sigma)
         return c / c[-1]
+
+
+# ---------------------------------------------------------------------------------------------------
+# GaussianProcessInference (SURVEY 8(f) row 2): restatement of include/GaussianProcessInference.h
+# ---------------------------------------------------------------------------------------------------
+def pinv_abs(m, epsilon=np.finfo(np.float64).eps):
+    """include/Prior.h:38-57: SVD pseudo-inverse, singular values <= epsilon (ABSOLUTE) are dropped."""
+    m = np.atleast_2d(np.asarray(m, dtype=np.float64))
+    u, s, vt = np.linalg.svd(m, full_matrices=True)
+    k = len(s)
+    inv = np.array([0.0 if v <= epsilon else 1.0 / v for v in s])
+    return (vt[:k].T * inv[None, :]) @ u[:, :k].T
+
+
+def _mm(A, B):
+    """Dense product with the plain i-k-j loop order of an unblocked row-major GEMM (what the reference's Eigen
+    expression evaluates to for these tiny operands). The order matters: pinv(g g^T) g cancels catastrophically
+    (entries of 1e14 producing an O(1) result), so the optimiser's step IS the rounding of this sum."""
+    A, B = np.atleast_2d(np.asarray(A, dtype=np.float64)), np.asarray(B, dtype=np.float64)
+    vec = B.ndim == 1
+    B2 = B[:, None] if vec else B
+    out = np.zeros((A.shape[0], B2.shape[1]))
+    for i in range(A.shape[0]):
+        for k in range(A.shape[1]):
+            a = A[i, k]
+            for j in range(B2.shape[1]):
+                out[i, j] += a * B2[k, j]
+    return out[:, 0] if vec else out
+
+
+def _signed_log(v):
+    return np.log(1 + v) if v >= 0 else -np.log(1 + abs(v))
+
+
+def infer_optimize(value_grad, params, step, iterations, pinv=None):
+    """GaussianProcessInference::Optimize (:84-156). value_grad(params) -> (value (M,), grad (P,)).
+    pinv: the pseudo-inverse to use (default pinv_abs; tests inject the reference's own gpr::pinv, because the
+    pseudo-inverse of the rank-1 matrix g g^T with an ABSOLUTE cut-off is dominated by the SVD's rounding noise and
+    differs between SVD implementations)."""
+    pinv = pinv or pinv_abs
+    params = [float(p) for p in params]
+    for _ in range(iterations):
+        value, grad = value_grad(params)
+        sign = -1.0 if value[0] > 0 else 1.0                                   # :95
+        update = _mm(pinv(np.outer(grad, grad)), grad)                         # :97
+        for p in range(len(params)):
+            if update[p] == 0:                                                 # :118-126
+                params[p] += step ** 3 * _signed_log(grad[p]) * sign
+            else:                                                              # :127-136
+                params[p] -= step * _signed_log(update[p] * value[0]) * sign
+    return params
+
+
+def infer_optimize2(value_jac, params, step, iterations, mask=None, pinv=None):
+    """GaussianProcessInference::Optimize2 (:158-229). value_jac(params) -> (value (M,), J (M, P))."""
+    pinv = pinv or pinv_abs
+    params = [float(p) for p in params]
+    mask = [True] * len(params) if mask is None else list(mask)
+    previous = None
+    for it in range(iterations):
+        value, J = value_jac(params)
+        value = np.array(value, dtype=np.float64)
+        if it > 0 and np.linalg.norm(previous - value) == 0:                   # :169-174
+            break
+        value = np.where(value > 0, -value, value)                             # :176-179
+        update = _mm(_mm(pinv(_mm(J.T, J)), J.T), value)                       # :182
+        for p in range(len(params)):
+            if mask[p]:                                                        # :195-203
+                params[p] -= step * _signed_log(update[p])
+        previous = value
+    return params

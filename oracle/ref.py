@@ -218,10 +218,33 @@ class RefGP:
         _ck(lib().ref_loglik_value_jac(self.h, _p(v), _p(J)))
         return v, J
 
+    def set_params(self, p):
+        p = _f(p).ravel()
+        _ck(lib().ref_gp_set_params(self.h, _p(p), p.size))
+        return self
+
+    def infer(self, which, step, iterations, P, mask=None):
+        """GaussianProcessInference::Optimize (which=1) / Optimize2 (which=2) of the reference; returns GetParameters()."""
+        out = np.empty(P)
+        n = C.c_int()
+        m = None if mask is None else np.ascontiguousarray(mask, dtype=np.int32)
+        lib().ref_infer.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        _ck(lib().ref_infer(self.h, int(which), float(step), int(iterations), None if m is None else _p(m),
+                            0 if m is None else len(m), _p(out), C.byref(n)))
+        return out[:n.value]
+
     def lik_value(self):
         v = np.empty(self.M)
         _ck(lib().ref_lik_value(self.h, _p(v)))
         return v
+
+
+def pinv(A):
+    """gpr::pinv (include/Prior.h:38-57)."""
+    A = _f(np.atleast_2d(A))
+    out = np.empty((A.shape[1], A.shape[0]))
+    _ck(lib().ref_pinv(_p(A), A.shape[0], A.shape[1], _p(out)))
+    return out
 
 
 class RefPCA:

@@ -13,6 +13,7 @@
 #include <string>
 
 #include "lib/GaussianProcess.cpp"  // -I/root/reference
+#include "include/GaussianProcessInference.h"  // the optimiser loop; boost stand-ins in eigen_lite
 #include "include/PCA.h"          // the reference's PCA, BDCSVD -> LAPACK dgesdd in eigen_lite
 
 // ---- LAPACK: the reference declares the un-prefixed Fortran symbols; scipy's OpenBLAS exports them
@@ -321,6 +322,47 @@ int ref_pca_reconstruct(void* p, const double* W, long nF, long ncols, double* o
         std::memcpy(Wm.data(), W, sizeof(double) * nF * ncols);
         Mat R = pca->GetReconstruction(Wm);
         from_mat(R, out);
+    });
+}
+
+
+// ---- GaussianProcessInference (include/GaussianProcessInference.h:84-229) -------------------------------------
+// which = 1: Optimize, 2: Optimize2. mask (may be NULL): SetParametersToOptimize. params_out: the P parameters after
+// `iterations` iterations (GetParameters); the GP's kernel is left at the last parameters the loop evaluated.
+int ref_infer(void* h, int which, double step, int iterations, const int* mask, int nmask, double* params_out,
+              int* nparams) {
+    return guard([&] {
+        typedef gpr::GaussianProcessInference<double> Inference;
+        Inference::LikelihoodTypePointer lh(new gpr::GaussianLogLikelihood<double>());
+        Inference gpi(lh, borrow(h), step, (unsigned)iterations);
+        if (mask) {
+            Inference::BooleanVectorType bv;
+            for (int i = 0; i < nmask; ++i) bv.push_back(mask[i] != 0);
+            gpi.SetParametersToOptimize(bv);
+        }
+        if (which == 2) gpi.Optimize2(false, false);
+        else gpi.Optimize(false, false);
+        Inference::ParameterVectorType p = gpi.GetParameters();
+        *nparams = (int)p.size();
+        for (size_t i = 0; i < p.size(); ++i) params_out[i] = p[i];
+    });
+}
+// pinv of include/Prior.h:38-57 on an r x c row-major matrix -> c x r
+int ref_pinv(const double* A, int r, int c, double* out) {
+    return guard([&] {
+        Mat M(r, c);
+        std::memcpy(M.data(), A, sizeof(double) * r * c);
+        Mat P = gpr::pinv<Mat>(M);
+        from_mat(P, out);
+    });
+}
+
+
+// kernel->SetParameters(p) on the GP's kernel, as the optimiser loop does every iteration (GaussianProcessInference.h:90)
+int ref_gp_set_params(void* h, const double* p, int n) {
+    return guard([&] {
+        std::vector<double> v(p, p + n);
+        static_cast<Access*>(h)->GetKernel()->SetParameters(v);
     });
 }
 

@@ -32,6 +32,14 @@ def test_cxx_pca_program():
     assert rc == 0 and "[failed]" not in out, out[-4000:]
 
 
+def test_cxx_inference_program():
+    """GaussianProcessInference<T> over the device-resident likelihood (tests/cxx/inference_device_test.cpp)."""
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "inference_device_test")
+    assert os.path.exists(exe), "tests/cxx/bin/inference_device_test missing: run __graft_entry__.build()"
+    rc, out = _run(exe)
+    assert rc == 0 and "[failed]" not in out, out[-4000:]
+
+
 DROPIN = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "dropin", "*")))
 
 
