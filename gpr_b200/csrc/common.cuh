@@ -32,6 +32,10 @@ struct GemmArgs {
     // of the PCA Gram, pca.cu). 0 and 1 both mean a single GEMM.
     int batch;
     int64_t sA, sB, sC;
+    // ktri: triangular operand structure known to the caller; the k loop of a tile starts later (rounded down to BK):
+    //   1: B (K x N) is lower triangular, B[k][n] = 0 for k < n  ->  k starts at the tile's first column (TRMM, NN)
+    //   2: A and B (K x M, K x N) are lower triangular            ->  k starts at max(first row, first column) (LAUUM, TN)
+    int ktri;
 };
 
 enum GemmForm { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };
@@ -74,6 +78,7 @@ struct Ctx {
     int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu
     int64_t opt_gemm_variant = -1; // -1: auto; 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
+    int64_t opt_inverse_long_k = 1;       // explicit inverse as TRTRI + LAUUM with long-K GEMMs (solve.cu)
     int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
     cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel
     int64_t opt_profile = 0;      // time every trailing-update GEMM launch with CUDA events (bench.py roofline)

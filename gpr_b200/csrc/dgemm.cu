@@ -180,10 +180,14 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     const int grp = lane >> 2, t4 = lane & 3;
 
     const int64_t z = blockIdx.y;  // batch index (0 for a single GEMM; the strides are then unused)
-    const double* Abase = (AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0)) + z * g.sA;
-    const double* Bbase = (BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0)) + z * g.sB;
+    // triangular operands: skip the leading k range that is known to be zero (whole BK steps only)
+    const int kskip = (g.ktri == 1 ? n0 : (g.ktri == 2 ? max(m0, n0) : 0)) / BK * BK;
+    const int Kt = g.K - kskip;  // this tile's contraction depth
+    if (Kt <= 0 && g.beta == 1.0) return;
+    const double* Abase = (AKC ? (g.A + (int64_t)m0 * g.lda + kskip) : (g.A + m0 + (int64_t)kskip * g.lda)) + z * g.sA;
+    const double* Bbase = (BKC ? (g.B + (int64_t)n0 * g.ldb + kskip) : (g.B + n0 + (int64_t)kskip * g.ldb)) + z * g.sB;
     const int mrem = g.M - m0, nrem = g.N - n0;
-    const int nk = (g.K + BK - 1) / BK;
+    const int nk = Kt > 0 ? (Kt + BK - 1) / BK : 0;
 
     FastLoader<BM, AKC, THREADS> fa;
     FastLoader<BN, BKC, THREADS> fb;
@@ -194,15 +198,15 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     auto issue = [&](int kt) {
         const int buf = kt % STAGES;
         const int k0 = kt * BK;
-        if (interior && k0 + BK <= g.K) {
+        if (interior && k0 + BK <= Kt) {
             fa.issue(AKC ? (int64_t)k0 : (int64_t)k0 * g.lda, (unsigned)(buf * TA::ELEMS * sizeof(double)));
             fb.issue(BKC ? (int64_t)k0 : (int64_t)k0 * g.ldb, (unsigned)(buf * TB::ELEMS * sizeof(double)));
             return;
         }
         const double* a = AKC ? (Abase + k0) : (Abase + (int64_t)k0 * g.lda);
         const double* b = BKC ? (Bbase + k0) : (Bbase + (int64_t)k0 * g.ldb);
-        TA::template load<THREADS>(sA + buf * TA::ELEMS, a, g.lda, mrem, g.K - k0, tid);
-        TB::template load<THREADS>(sB + buf * TB::ELEMS, b, g.ldb, nrem, g.K - k0, tid);
+        TA::template load<THREADS>(sA + buf * TA::ELEMS, a, g.lda, mrem, Kt - k0, tid);
+        TB::template load<THREADS>(sB + buf * TB::ELEMS, b, g.ldb, nrem, Kt - k0, tid);
     };
 
     double acc[FM][FN][2];

@@ -356,6 +356,57 @@ int trsm_lower_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int
                                           : bwd_right(c, L, ldl, invL, N, B, ldb, M);
 }
 
+// K5, long-K form (default): C = W^T W with W = L^-1, both halves as GEMMs with a long contraction.
+//   TRTRI, left-looking over super-rows S of 512 rows: W[S, :s0] <- L[S, :s0] W[:s0, :s0] is ONE product of depth
+//          s0 whose k loop skips the zero part of the triangular W (GemmArgs::ktri = 1); inside the super-row
+//          the four 128-row blocks are finished with short updates and the pre-inverted diagonal blocks.
+//   LAUUM, one launch: C[m][n] = sum_{k >= max(m, n)} W[k][m] W[k][n], lower tiles only (ktri = 2).
+// N^3/3 flop each, like the structured right-looking sweeps below, but those update all of C once per 128 columns
+// (K = 128 per pass, ~N^3/48 bytes of read-modify-write traffic); here every output tile is written once.
+static int inverse_long_k(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* C, int64_t ldc) {
+    double* W = nullptr;
+    GP_CUDA(c, cudaMallocAsync((void**)&W, sizeof(double) * N * ldc, c->stream));
+    auto body = [&]() -> int {
+        GP_TRY(fill2d(c, W, ldc, N, N, 0.0));
+        constexpr int64_t WS = 512;
+        for (int64_t s0 = 0; s0 < N; s0 += WS) {
+            const int64_t ws = (N - s0 < WS) ? (N - s0) : WS;
+            if (s0 > 0) {
+                GemmArgs t{};
+                t.A = L + s0 * ldl; t.lda = ldl; t.B = W; t.ldb = ldc; t.C = W + s0 * ldc; t.ldc = ldc;
+                t.M = (int)ws; t.N = (int)s0; t.K = (int)s0; t.alpha = 1.0; t.beta = 0.0; t.ktri = 1;
+                GP_TRY(gemm(c, GEMM_NN, t));
+            }
+            for (int64_t r0 = s0; r0 < s0 + ws; r0 += NB) {
+                const int n = (int)((N - r0 < NB) ? (N - r0) : NB);
+                const double* invk = invL + (r0 / NB) * (int64_t)NB * NB;
+                double* Wr = W + r0 * ldc;
+                if (r0 > s0) {  // X_r += L[r, s0:r0] W[s0:r0, :r0]
+                    GemmArgs u{};
+                    u.A = L + r0 * ldl + s0; u.lda = ldl; u.B = W + s0 * ldc; u.ldb = ldc; u.C = Wr; u.ldc = ldc;
+                    u.M = n; u.N = (int)r0; u.K = (int)(r0 - s0); u.alpha = 1.0; u.beta = 1.0;
+                    GP_TRY(gemm(c, GEMM_NN, u));
+                }
+                if (r0 > 0) {  // W[r, :r0] = -inv(L_rr) X_r, in place (one row tile: every CTA owns its columns)
+                    GemmArgs d{};
+                    d.A = invk; d.lda = NB; d.B = Wr; d.ldb = ldc; d.C = Wr; d.ldc = ldc;
+                    d.M = n; d.N = (int)r0; d.K = n; d.alpha = -1.0; d.beta = 0.0;
+                    GP_TRY(gemm(c, GEMM_NN, d));
+                }
+                GP_TRY(copy2d(c, Wr + r0, ldc, invk, NB, n, n));
+            }
+        }
+        GemmArgs l{};
+        l.A = W; l.lda = ldc; l.B = W; l.ldb = ldc; l.C = C; l.ldc = ldc;
+        l.M = (int)N; l.N = (int)N; l.K = (int)N; l.alpha = 1.0; l.beta = 0.0; l.lower = 1; l.ktri = 2;
+        GP_TRY(gemm(c, GEMM_TN, l));
+        return symmetrize_from_lower(c, C, ldc, N);
+    };
+    const int rc = body();
+    cudaFreeAsync(W, c->stream);
+    return rc;
+}
+
 // K5: C = (L L^T)^-1 from the factor, 2 N^3 / 3 flop (LAPACK dpotri's count; the reference calls dgetri / dpotri,
 // include/LAPACKUtils.h:50, :65). Two structured sweeps over C = I:
 //   forward  W = L^-1 is lower triangular: at block row k only columns [0, k0 + n) can be non-zero, so both GEMMs
@@ -363,6 +414,7 @@ int trsm_lower_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int
 //   backward C = L^-T W is symmetric: only its lower triangle is formed (row block i needs columns <= i), the
 //            update of the rows above block k is a lower-tiles-only GEMM (N^3 / 3 flop), then mirrored.
 int inverse_from_factor(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* C, int64_t ldc) {
+    if (c->opt_inverse_long_k && N > 2 * NB) return inverse_long_k(c, L, ldl, invL, N, C, ldc);
     GP_TRY(set_identity(c, C, ldc, N));
     for (int64_t k0 = 0; k0 < N; k0 += NB) {
         const int n = (int)((N - k0 < NB) ? (N - k0) : NB);
