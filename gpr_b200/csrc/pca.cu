@@ -67,22 +67,23 @@ __global__ void __launch_bounds__(PT) pca_center_kernel(const double* __restrict
     for (int j = lane; j < n; j += 32) z[j] = x[j] - mu;
 }
 
-// G = sum_z P_z in a fixed order, symmetrised; written into the n2 x n2 Jacobi work matrix (zero padded)
-__global__ void pca_gram_reduce_kernel(const double* __restrict__ P, int batch, int n, int64_t ldp, int64_t strideP,
-                                       double* __restrict__ G, int n2) {
-    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// G = sum_z P_z, symmetrised; written into the n2 x n2 Jacobi work matrix (zero padded). One warp per element:
+// lanes stride the batch, fixed-order shuffle tree (deterministic; the batch can be ~300 deep for small n).
+__global__ void __launch_bounds__(256) pca_gram_reduce_kernel(const double* __restrict__ P, int batch, int n, int64_t ldp,
+                                                              int64_t strideP, double* __restrict__ G, int n2) {
+    const int lane = threadIdx.x & 31;
+    const int64_t e = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (e >= (int64_t)n2 * n2) return;
     const int i = (int)(e / n2), j = (int)(e % n2);
     double v = 0.0;
     if (i < n && j < n) {
-        double a = 0.0, b = 0.0;
-        for (int z = 0; z < batch; ++z) {
-            a += P[z * strideP + (int64_t)i * ldp + j];
-            b += P[z * strideP + (int64_t)j * ldp + i];
-        }
-        v = 0.5 * (a + b);
+        for (int z = lane; z < batch; z += 32)
+            v += P[z * strideP + (int64_t)i * ldp + j] + P[z * strideP + (int64_t)j * ldp + i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        v *= 0.5;
     }
-    G[e] = v;
+    if (lane == 0) G[e] = v;
 }
 
 // ---- parallel two-sided Jacobi on the n2 x n2 symmetric matrix A (n2 even), eigenvectors accumulated in V -----
@@ -382,7 +383,7 @@ int project_chunk(PcaModel* m, const double* B, int64_t ldb, int K, const double
                   const double* dX, int64_t ldx, int T, double* dF, int64_t ldf) {
     Ctx* c = m->c;
     const int kblocks = (K + 31) / 32;
-    int64_t splits = std::max<int64_t>(1, (148 * 6 + kblocks - 1) / kblocks);
+    int64_t splits = std::max<int64_t>(1, (148 * 3 + kblocks - 1) / kblocks);  // one resident wave (3 CTAs/SM at 82 regs)
     splits = std::min<int64_t>(splits, std::max<int64_t>(1, m->D / 256));
     const int64_t rps = (m->D + splits - 1) / splits;
     splits = (m->D + rps - 1) / rps;
@@ -553,7 +554,7 @@ int fit_dev(PcaModel* m, const double* dX, int64_t ldx, int64_t D, int64_t n, in
             g.M = (int)n; g.N = (int)n; g.K = (int)slab; g.alpha = 1.0; g.beta = 0.0;
             g.batch = (int)batch; g.sA = slab * m->ldu; g.sB = slab * m->ldu; g.sC = n * ldg;
             GP_TRY(gemm(c, GEMM_TN, g));
-            pca_gram_reduce_kernel<<<(unsigned)(((int64_t)n2 * n2 + 255) / 256), 256, 0, c->stream>>>(dPart, (int)batch, (int)n,
+            pca_gram_reduce_kernel<<<(unsigned)(((int64_t)n2 * n2 + 7) / 8), 256, 0, c->stream>>>(dPart, (int)batch, (int)n,
                                                                                                     ldg, n * ldg, dA, n2);
             ++c->launches;
             GP_CUDA(c, cudaGetLastError());
