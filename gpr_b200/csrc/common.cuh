@@ -78,6 +78,7 @@ struct Ctx {
     int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu
     int64_t opt_gemm_variant = -1; // -1: auto; 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
+    int64_t opt_trsv_chain = 1;           // M <= 2 triangular solves as one chained launch (solve.cu)
     int64_t opt_inverse_long_k = 1;       // explicit inverse as TRTRI + LAUUM with long-K GEMMs (solve.cu)
     int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
     cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel

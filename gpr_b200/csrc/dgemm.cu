@@ -159,7 +159,9 @@ __device__ __forceinline__ bool map_tile(int lin, int lower, int tiles_m, int ti
 
 // STAGES k-tiles of BK live in the shared-memory ring; KSTEP of them are consumed per CTA barrier
 // (KSTEP = 2 halves the barrier rate at the same BK = 16 tile geometry).
-template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
+// EXT = false is the Cholesky / solve hot path: no batch index, no triangular k range (the 64x16 variant sits exactly at
+// its 128-register cap; carrying the extra strides and offsets cost 3 % of the factorisation when it was unconditional).
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1, bool EXT = false>
 __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel(GemmArgs g, int tiles_m, int tiles_n) {
     constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
     constexpr int WARPS_N = BN / WN;
@@ -179,15 +181,18 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
     const int grp = lane >> 2, t4 = lane & 3;
 
-    const int64_t z = blockIdx.y;  // batch index (0 for a single GEMM; the strides are then unused)
+    const int64_t z = EXT ? blockIdx.y : 0;  // batch index
     // triangular operands: skip the leading k range that is known to be zero (whole BK steps only)
-    const int kskip = (g.ktri == 1 ? n0 : (g.ktri == 2 ? max(m0, n0) : 0)) / BK * BK;
-    const int Kt = g.K - kskip;  // this tile's contraction depth
-    if (Kt <= 0 && g.beta == 1.0) return;
-    const double* Abase = (AKC ? (g.A + (int64_t)m0 * g.lda + kskip) : (g.A + m0 + (int64_t)kskip * g.lda)) + z * g.sA;
-    const double* Bbase = (BKC ? (g.B + (int64_t)n0 * g.ldb + kskip) : (g.B + n0 + (int64_t)kskip * g.ldb)) + z * g.sB;
+    const int kskip = EXT ? (g.ktri == 1 ? n0 : (g.ktri == 2 ? max(m0, n0) : 0)) / BK * BK : 0;
+    const int Kt = EXT ? g.K - kskip : g.K;  // this tile's contraction depth
+    const double* Abase = AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0);
+    const double* Bbase = BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0);
+    if (EXT) {
+        Abase += (AKC ? (int64_t)kskip : (int64_t)kskip * g.lda) + z * g.sA;
+        Bbase += (BKC ? (int64_t)kskip : (int64_t)kskip * g.ldb) + z * g.sB;
+    }
     const int mrem = g.M - m0, nrem = g.N - n0;
-    const int nk = Kt > 0 ? (Kt + BK - 1) / BK : 0;
+    const int nk = (Kt + BK - 1) / BK;  // Kt > 0: callers keep kskip < K
 
     FastLoader<BM, AKC, THREADS> fa;
     FastLoader<BN, BKC, THREADS> fb;
@@ -263,7 +268,7 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     for (int i = 0; i < FM; ++i) {
         const int row = m0 + wm0 + i * 8 + grp;
         if (row >= g.M) continue;
-        double* crow = g.C + z * g.sC + (int64_t)row * g.ldc;
+        double* crow = g.C + (EXT ? z * g.sC : 0) + (int64_t)row * g.ldc;
 #pragma unroll
         for (int j = 0; j < FN; ++j) {
             const int col = n0 + wn0 + j * 8 + t4 * 2;
@@ -286,13 +291,13 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
-static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP, bool EXT>
+static int launch_impl(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
     using TA = OperandTile<BM, AKC>;
     using TB = OperandTile<BN, BKC>;
     constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
     constexpr size_t SMEM = sizeof(double) * STAGES * (TA::ELEMS + TB::ELEMS);
-    auto kern = dgemm_kernel<BM, BN, WM, WN, AKC, BKC, STAGES, MINB, KSTEP>;
+    auto kern = dgemm_kernel<BM, BN, WM, WN, AKC, BKC, STAGES, MINB, KSTEP, EXT>;
     GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     const int64_t tm = (g.M + BM - 1) / BM, tn = (g.N + BN - 1) / BN;
     int64_t grid;
@@ -308,6 +313,16 @@ static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     return 0;
+}
+
+// the extended kernel (batch / triangular k range) exists only for the default tile shapes
+template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
+static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
+    if (g.batch > 1 || g.ktri != 0) {
+        if (KSTEP == 1 && STAGES == 3) return launch_impl<BM, BN, WM, WN, AKC, BKC, 3, MINB, 1, true>(c, g, stream);
+        return fail(c, -2, "gemm: batch / triangular k range need the default pipeline (gemm_stages = 3, variant 0 or 1)");
+    }
+    return launch_impl<BM, BN, WM, WN, AKC, BKC, STAGES, MINB, KSTEP, false>(c, g, stream);
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -338,30 +353,18 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
             if (wide) return launch<128, 128, 64, 32, true, true, 3, 1>(c, g, stream);
             if (variant == 1) return launch<128, 64, 64, 16, true, true, 3, 2>(c, g, stream);
             if (variant == 2) return launch<128, 64, 64, 32, true, true, 4, 2, 2>(c, g, stream);
-            if (variant == 3) return launch<128, 64, 64, 16, true, true, 4, 2, 2>(c, g, stream);
-            if (variant == 4) return launch<128, 128, 64, 32, true, true, 4, 1>(c, g, stream);
-            if (variant == 5) return launch<128, 128, 64, 16, true, true, 4, 1>(c, g, stream);
-            if (variant == 6) return launch<128, 128, 64, 16, true, true, 6, 1, 2>(c, g, stream);
             return s3 ? launch<128, 64, 64, 32, true, true, 3, 2>(c, g, stream)
                       : launch<128, 64, 64, 32, true, true, 4, 2>(c, g, stream);
         case GEMM_NN:
             if (wide) return launch<128, 128, 64, 32, true, false, 3, 1>(c, g, stream);
             if (variant == 1) return launch<128, 64, 64, 16, true, false, 3, 2>(c, g, stream);
             if (variant == 2) return launch<128, 64, 64, 32, true, false, 4, 2, 2>(c, g, stream);
-            if (variant == 3) return launch<128, 64, 64, 16, true, false, 4, 2, 2>(c, g, stream);
-            if (variant == 4) return launch<128, 128, 64, 32, true, false, 4, 1>(c, g, stream);
-            if (variant == 5) return launch<128, 128, 64, 16, true, false, 4, 1>(c, g, stream);
-            if (variant == 6) return launch<128, 128, 64, 16, true, false, 6, 1, 2>(c, g, stream);
             return s3 ? launch<128, 64, 64, 32, true, false, 3, 2>(c, g, stream)
                       : launch<128, 64, 64, 32, true, false, 4, 2>(c, g, stream);
         case GEMM_TN:
             if (wide) return launch<128, 128, 64, 32, false, false, 3, 1>(c, g, stream);
             if (variant == 1) return launch<128, 64, 64, 16, false, false, 3, 2>(c, g, stream);
             if (variant == 2) return launch<128, 64, 64, 32, false, false, 4, 2, 2>(c, g, stream);
-            if (variant == 3) return launch<128, 64, 64, 16, false, false, 4, 2, 2>(c, g, stream);
-            if (variant == 4) return launch<128, 128, 64, 32, false, false, 4, 1>(c, g, stream);
-            if (variant == 5) return launch<128, 128, 64, 16, false, false, 4, 1>(c, g, stream);
-            if (variant == 6) return launch<128, 128, 64, 16, false, false, 6, 1, 2>(c, g, stream);
             return s3 ? launch<128, 64, 64, 32, false, false, 3, 2>(c, g, stream)
                       : launch<128, 64, 64, 32, false, false, 4, 2>(c, g, stream);
     }

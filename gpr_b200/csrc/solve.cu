@@ -288,9 +288,204 @@ static int trsv_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, in
     return 0;
 }
 
+// ---- chained TRSV: the whole sweep in ONE launch (M <= 2) -------------------------------------------------------------
+// One CTA per 128-row block. A CTA takes its block index from an atomic ticket, so a block only ever waits for
+// blocks whose CTAs started earlier (no deadlock whatever the residency), streams its off-diagonal blocks of L while
+// the blocks before it are still being solved, and publishes x_j with a flag. The dependent chain per block is one
+// flag poll, one 128-value load, one 128 x 128 block product and the pre-inverted diagonal block from shared memory:
+// ~3 us instead of one ~25 us launch per block (the step kernels above). Deterministic: fixed summation order.
+//   forward  x_j = inv(L_jj)   (b_j - sum_{k<j} L_jk x_k)     lane = 4 columns of L_jk, warp = 8 rows, shuffle fold
+//   backward x_j = inv(L_jj)^T (z_j - sum_{k>j} L_kj^T x_k)   lane = 4 columns (outputs), warp = 8 rows, smem fold
+constexpr int TC_THREADS = 512;
+constexpr int TC_LD = NB + 1;
+
+__device__ __forceinline__ void tc_wait(volatile int* flag) {
+    if ((threadIdx.x & 31) == 0)
+        while (*flag == 0) {}
+    __syncwarp();
+    __threadfence();
+}
+
+template <int NC, bool BWD>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+trsv_chain_kernel(const double* __restrict__ L, int64_t ldl, const double* __restrict__ invL, int64_t N, double* B,
+                  int64_t ldb, int nblk, int* ticket, volatile int* flags) {
+    extern __shared__ double tcs[];
+    double* S = tcs;                       // [NB][TC_LD]: S[i][t] multiplies y[i] into output t
+    double* ys = S + NB * TC_LD;           // [NB][NC]
+    double* red = ys + NB * NC;            // [16][NB][NC] (backward) / [4][NB][NC] (final product partials)
+    __shared__ int s_ticket;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_ticket = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int j = BWD ? (nblk - 1 - s_ticket) : s_ticket;
+    const int64_t j0 = (int64_t)j * NB;
+    const int n = (int)min((int64_t)NB, N - j0);
+    {   // diagonal inverse into shared memory: forward needs inv[t][i] at S[i][t], backward inv[i][t]
+        const double* inv = invL + (int64_t)j * NB * NB;
+        for (int e = tid; e < NB * NB; e += TC_THREADS) {
+            const int r = e / NB, cidx = e - r * NB;
+            const double v = inv[e];
+            if (BWD) S[r * TC_LD + cidx] = v;
+            else S[cidx * TC_LD + r] = v;
+        }
+    }
+    const int r8 = warp * 8, c4 = lane * 4;
+    if (!BWD) {
+        double acc[8][NC];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[i][c] = 0.0;
+        for (int k = 0; k < j; ++k) {
+            double2 lo[8], hi[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                lo[i] = hi[i] = make_double2(0.0, 0.0);
+                if (r8 + i < n) {
+                    const double2* src = reinterpret_cast<const double2*>(L + (j0 + r8 + i) * ldl + (int64_t)k * NB + c4);
+                    lo[i] = __ldg(src);
+                    hi[i] = __ldg(src + 1);
+                }
+            }
+            tc_wait(flags + k);
+            double x[4][NC];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int c = 0; c < NC; ++c) x[q][c] = __ldcg(B + ((int64_t)k * NB + c4 + q) * ldb + c);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int c = 0; c < NC; ++c)
+                    acc[i][c] = fma(hi[i].y, x[3][c], fma(hi[i].x, x[2][c], fma(lo[i].y, x[1][c], fma(lo[i].x, x[0][c], acc[i][c]))));
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                double v = acc[i][c];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) ys[(r8 + i) * NC + c] = v;
+            }
+        __syncthreads();
+    } else {
+        double acc[4][NC];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[q][c] = 0.0;
+        for (int k = nblk - 1; k > j; --k) {
+            const int64_t k0 = (int64_t)k * NB;
+            double2 lo[8], hi[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                lo[i] = hi[i] = make_double2(0.0, 0.0);
+                if (k0 + r8 + i < N) {
+                    const double2* src = reinterpret_cast<const double2*>(L + (k0 + r8 + i) * ldl + j0 + c4);
+                    lo[i] = __ldg(src);
+                    hi[i] = __ldg(src + 1);
+                }
+            }
+            tc_wait(flags + k);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (k0 + r8 + i < N) {
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const double xv = __ldcg(B + (k0 + r8 + i) * ldb + c);
+                        acc[0][c] = fma(lo[i].x, xv, acc[0][c]);
+                        acc[1][c] = fma(lo[i].y, xv, acc[1][c]);
+                        acc[2][c] = fma(hi[i].x, xv, acc[2][c]);
+                        acc[3][c] = fma(hi[i].y, xv, acc[3][c]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int c = 0; c < NC; ++c) red[(warp * NB + c4 + q) * NC + c] = acc[q][c];
+        __syncthreads();
+        if (tid < NB) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                double v = 0.0;
+#pragma unroll
+                for (int w = 0; w < TC_THREADS / 32; ++w) v += red[(w * NB + tid) * NC + c];
+                ys[tid * NC + c] = v;
+            }
+        }
+        __syncthreads();
+    }
+    // y = b_j - sum (rows >= n of a ragged last block stay zero)
+    if (tid < NB) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) ys[tid * NC + c] = (tid < n) ? B[(j0 + tid) * ldb + c] - ys[tid * NC + c] : 0.0;
+    }
+    __syncthreads();
+    // x_j[t] = sum_i S[i][t] y[i]: four threads per output (32 terms each), folded through shared memory
+    {
+        const int t = tid & (NB - 1), part = tid >> 7;
+        double v[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) v[c] = 0.0;
+#pragma unroll 8
+        for (int i = part * 32; i < part * 32 + 32; ++i) {
+            const double sv = S[i * TC_LD + t];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) v[c] = fma(sv, ys[i * NC + c], v[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) red[(part * NB + t) * NC + c] = v[c];
+    }
+    __syncthreads();
+    if (tid < n) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const double v = (red[(0 * NB + tid) * NC + c] + red[(1 * NB + tid) * NC + c]) +
+                             (red[(2 * NB + tid) * NC + c] + red[(3 * NB + tid) * NC + c]);
+            B[(j0 + tid) * ldb + c] = v;
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();  // cumulative: the CTA's stores of x_j (ordered by the barrier) become visible before the flag
+        flags[j] = 1;
+    }
+}
+
+template <int NC>
+static int trsv_chain(Ctx* c, bool bwd, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb) {
+    const int nblk = (int)((N + NB - 1) / NB);
+    int* sync = nullptr;  // [0] ticket, [1 ..] flags
+    GP_CUDA(c, cudaMallocAsync((void**)&sync, sizeof(int) * (nblk + 1), c->stream));
+    GP_CUDA(c, cudaMemsetAsync(sync, 0, sizeof(int) * (nblk + 1), c->stream));
+    const size_t smem = sizeof(double) * ((size_t)NB * TC_LD + (size_t)NB * NC + (size_t)(TC_THREADS / 32) * NB * NC);
+    if (bwd) {
+        auto kern = trsv_chain_kernel<NC, true>;
+        GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<nblk, TC_THREADS, smem, c->stream>>>(L, ldl, invL, N, B, ldb, nblk, sync, sync + 1);
+    } else {
+        auto kern = trsv_chain_kernel<NC, false>;
+        GP_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<nblk, TC_THREADS, smem, c->stream>>>(L, ldl, invL, N, B, ldb, nblk, sync, sync + 1);
+    }
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    GP_CUDA(c, cudaFreeAsync(sync, c->stream));
+    return 0;
+}
+
 static int trsv_dispatch(Ctx* c, bool bwd, const double* L, int64_t ldl, const double* invL, int64_t N, double* B,
                          int64_t ldb, int64_t M) {
 #define GP_TRSV(NC) (bwd ? trsv_bwd<NC>(c, L, ldl, invL, N, B, ldb, (int)M) : trsv_fwd<NC>(c, L, ldl, invL, N, B, ldb, (int)M))
+    if (c->opt_trsv_chain && (ldl & 3) == 0 && N > NB) {  // 32-byte row segments need ldl % 4 == 0
+        if (M == 1) return trsv_chain<1>(c, bwd, L, ldl, invL, N, B, ldb);
+        if (M == 2) return trsv_chain<2>(c, bwd, L, ldl, invL, N, B, ldb);
+    }
     if (M <= 1) return GP_TRSV(1);
     if (M <= 2) return GP_TRSV(2);
     if (M <= 4) return GP_TRSV(4);

