@@ -137,6 +137,12 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
         if (c0 >= n) break;
         // ---- (1) warp 0: Cholesky of the diagonal block, lane i owns row i; then its inverse, lane j owns column j
         if (warp == 0) {
+            // Shared-memory broadcast instead of one shuffle per (column, row) pair: the ncu source view of the first
+            // version showed the other seven warps waiting at the barrier below for ~70 % of the kernel while this
+            // warp ran SHFL -> DFMA pairs back to back with the full shuffle latency exposed (~60 cycles per pair).
+            // Here a column is published once, read back with independent broadcast loads, then the FMAs run.
+            double* colb = Tm;                 // [2][32] column broadcast buffers (Tm is free during this phase)
+            double* rdb = Tm + 2 * P2_IB;      // [32] reciprocal diagonal
             double a[P2_IB];
 #pragma unroll
             for (int k = 0; k < P2_IB; ++k) a[k] = (k <= lane) ? S[(c0 + lane) * P2_LD + c0 + k] : 0.0;
@@ -153,11 +159,12 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
                 } else if (lane > j) {
                     a[j] = a[j] * rj;
                 }
+                double* cb = colb + (j & 1) * P2_IB;
+                cb[lane] = a[j];
+                __syncwarp();
 #pragma unroll
-                for (int k = j + 1; k < P2_IB; ++k) {
-                    const double lkj = __shfl_sync(FULL, a[j], k);
-                    if (lane >= k) a[k] = fma(-a[j], lkj, a[k]);
-                }
+                for (int k = j + 1; k < P2_IB; ++k)
+                    if (lane >= k) a[k] = fma(-a[j], cb[k], a[k]);  // broadcast loads, independent of the FMAs
             }
             if (fail_at >= 0) {
                 if (lane == 0) {
@@ -165,25 +172,28 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
                     atomicCAS(info, 0, col0 + c0 + fail_at + 1);
                 }
             } else {
+                // L_dd back to shared memory first: the inverse reads row i of L as broadcast loads
+#pragma unroll
+                for (int k = 0; k < P2_IB; ++k)
+                    if (k <= lane) S[(c0 + lane) * P2_LD + c0 + k] = a[k];
+                rdb[lane] = rdiag;
+                __syncwarp();
                 // inverse: column j of W = inv(L_dd): w[j] = 1 / l_jj, w[i] = -(sum_{k=j}^{i-1} l_ik w[k]) / l_ii
                 double w[P2_IB];
 #pragma unroll
                 for (int i = 0; i < P2_IB; ++i) {
+                    const double* Li = S + (c0 + i) * P2_LD + c0;
+                    const double ri = rdb[i];
                     double acc0 = 0.0, acc1 = 0.0;  // two chains halve the dependent FMA latency
 #pragma unroll
                     for (int k = 0; k < i; ++k) {
-                        const double lik = __shfl_sync(FULL, a[k], i);
                         if (k >= lane) {
-                            if (k & 1) acc1 = fma(lik, w[k], acc1);
-                            else acc0 = fma(lik, w[k], acc0);
+                            if (k & 1) acc1 = fma(Li[k], w[k], acc1);
+                            else acc0 = fma(Li[k], w[k], acc0);
                         }
                     }
-                    const double ri = __shfl_sync(FULL, rdiag, i);
                     w[i] = (i == lane) ? ri : ((i > lane) ? -(acc0 + acc1) * ri : 0.0);
                 }
-#pragma unroll
-                for (int k = 0; k < P2_IB; ++k)
-                    if (k <= lane) S[(c0 + lane) * P2_LD + c0 + k] = a[k];
 #pragma unroll
                 for (int i = 0; i < P2_IB; ++i) Wd[(b * P2_IB + i) * (P2_IB + 1) + lane] = w[i];
             }
