@@ -446,7 +446,8 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     int64_t NBO = c->opt_nbo;
-    if (NBO <= 0) NBO = (N <= 20480) ? 512 : 1024;  // measured on B200: 512 wins up to N = 16384, 1024 from 32768
+    // measured on B200 (tools/chol_sweep2.py): 256 wins at N = 8192, 512 at 16384, 768-1024 from 24576
+    if (NBO <= 0) NBO = (N <= 10240) ? 256 : ((N <= 20480) ? 512 : 1024);
     if (NBO < NB) NBO = NB;
     NBO = NBO / NB * NB;
     if (c->opt_chol_left && c->panel_stream && N > 2 * NBO) {
