@@ -57,6 +57,12 @@ _PROTOS = {
     "gprb200_dgram": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_loglik": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gprb200_quadform": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gprb200_sparse_set_inducing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double]),
+    "gprb200_sparse_set_jitter": (C.c_int, [C.c_void_p, C.c_double]),
+    "gprb200_sparse_learn": (C.c_int, [C.c_void_p]),
+    "gprb200_sparse_get_alpha": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gprb200_sparse_predict": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "gprb200_sparse_cov": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_pca_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "gprb200_pca_destroy": (C.c_int, [C.c_void_p]),
     "gprb200_pca_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),

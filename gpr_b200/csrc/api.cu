@@ -124,6 +124,7 @@ int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, in
                        ((Y && M > 0) == (c->dY != nullptr));
     if (!reuse) free_model(c);
     c->have_factor = c->have_alpha = c->have_core = c->core_is_loaded = false;
+    sparse_invalidate(c);
     c->N = N; c->d = d; c->M = (Y ? M : 0); c->sigma = sigma;
     c->ldy = round_up(c->M > 0 ? c->M : 1, 16);
     c->ldk = round_up(N, 16);
@@ -213,6 +214,7 @@ void invalidate(Ctx* c) {
     c->have_alpha = false;
     c->have_core = false;
     c->core_is_loaded = false;
+    sparse_invalidate(c);
 }
 
 // q[t] = Kx_t^T (K + s^2 I)^-1 Ky_t for T pairs; dKa/dKb: T x N cross-Gram (ld ldkx), may alias.
@@ -371,6 +373,7 @@ int gprb200_destroy(gprb200_handle h) {
     gprb200_ctx* c = h;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    sparse_destroy(c);
     free_model(c);
     cudaFree(c->dInfo);
     cudaFree(c->dScratch);

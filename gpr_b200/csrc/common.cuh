@@ -88,6 +88,8 @@ struct Ctx {
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // Predict phase timing (resolved lazily by gprb200_phase_ms)
     bool predict_time_pending = false;
+
+    void* sparse = nullptr;  // SparseModel (sparse.cu): inducing points and the two m x m factors
     double phase_ms[GPRB200_T_COUNT] = {0};
 };
 
@@ -141,6 +143,9 @@ int coldot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, i
            double* d_out /* cols */);
 int rowdot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, int64_t rows, int64_t cols,
            double* d_out /* rows */);
+// sparse.cu
+void sparse_invalidate(Ctx* c);
+void sparse_destroy(Ctx* c);
 // predict.cu
 int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out);
 

@@ -222,6 +222,21 @@ int gprb200_predict_reconstruct(gprb200_handle h, gprb200_pca_handle p, const do
 int gprb200_predict_reconstruct_dev(gprb200_handle h, gprb200_pca_handle p, const double* dXs, int64_t T, double* dFields,
                                     int64_t ldo, double* dWeights, int64_t ldw);
 
+/* ---- Sparse (inducing-point) GP (reference include/SparseGaussianProcess.h) ----
+ * The dense samples are the handle's training set (set_train), the inducing points are added here. m <= n.
+ * Regression part only: PreComputeRegression, Predict, operator()(x, y); the sparse likelihood is not provided. */
+/* AddInducingSample x m (:61-76) + SetJitter (:118-121); Xm: m x d */
+int gprb200_sparse_set_inducing(gprb200_handle h, const double* Xm, int64_t m, int d, double jitter);
+int gprb200_sparse_set_jitter(gprb200_handle h, double jitter);
+/* Initialize -> PreComputeRegression (:124-141, :274-312): K = k(Xm,Xm) + jitter I, Knm, S = K + sigma^-2 Kmn Knm,
+ * alpha = sigma^-2 S^-1 Kmn Y (the value the reference's K^-1 (sigma^-2 K Sigma Kmn Y) reduces to). */
+int gprb200_sparse_learn(gprb200_handle h);
+int gprb200_sparse_get_alpha(gprb200_handle h, double* alpha); /* m x M regression vectors */
+/* Predict (:84-90) for T points: mean T x M (may be NULL); var (may be NULL): operator()(x, x) per point */
+int gprb200_sparse_predict(gprb200_handle h, const double* Xs, int64_t T, double* mean, double* var);
+/* operator()(x, y) (:92-106) for T pairs: k(x,y) - Kx^T K^-1 Ky + Kx^T S^-1 Ky */
+int gprb200_sparse_cov(gprb200_handle h, const double* Xa, const double* Xb, int64_t T, double* cov);
+
 #ifdef __cplusplus
 }
 #endif

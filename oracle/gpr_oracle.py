@@ -405,3 +405,34 @@ def infer_optimize2(value_jac, params, step, iterations, mask=None, pinv=None):
                 params[p] -= step * _signed_log(update[p])
         previous = value
     return params
+
+
+# ---------------------------------------------------------------------------------------------------
+# SparseGaussianProcess, regression part: restatement of include/SparseGaussianProcess.h
+# ---------------------------------------------------------------------------------------------------
+class SparseOracle:
+    """PreComputeRegression (:274-312), Predict (:84-90), operator() (:92-106) with the reference's explicit
+    inverses (LU, include/LAPACKUtils.h:85-97) and its order of products."""
+
+    def __init__(self, kernel, X, Y, Xm, sigma, jitter):
+        self.k = parse_kernel(kernel) if isinstance(kernel, str) else kernel
+        self.X, self.Y, self.Xm = (np.asarray(a, dtype=np.float64) for a in (X, Y, Xm))
+        K = kernel_matrix(self.k, self.Xm, self.Xm) + jitter * np.eye(len(self.Xm))    # :175-180
+        self.Kinv = lu_invert(K)                                                        # :283
+        Knm = kernel_matrix(self.k, self.X, self.Xm)                                    # :285-286 (n x m)
+        is2 = 1.0 / (sigma * sigma)
+        S = K + is2 * Knm.T @ Knm                                                       # :292
+        self.Sigma = lu_invert(S)                                                       # :293
+        self.alpha = self.Kinv @ (is2 * K @ self.Sigma @ Knm.T @ self.Y)                # :296
+        self.R = self.Kinv @ (K @ self.Sigma @ K) @ self.Kinv                           # :299
+
+    def kx(self, x):
+        return kernel_matrix(self.k, np.atleast_2d(x), self.Xm)[0]
+
+    def predict(self, x):
+        return self.kx(x) @ self.alpha
+
+    def cov(self, x, y):
+        kx, ky = self.kx(x), self.kx(y)
+        kxy = kernel_matrix(self.k, np.atleast_2d(x), np.atleast_2d(y))[0, 0]
+        return kxy - kx @ self.Kinv @ ky + kx @ self.R @ ky

@@ -239,6 +239,49 @@ class RefGP:
         return v
 
 
+class RefSparseGP:
+    """The reference's SparseGaussianProcess<double> (include/SparseGaussianProcess.h) through oracle/_ref."""
+
+    def __init__(self, kernel_string, sigma, jitter):
+        L = lib()
+        L.ref_sgp_new.restype = C.c_void_p
+        L.ref_sgp_new.argtypes = [C.c_char_p, C.c_double, C.c_double]
+        L.ref_sgp_free.argtypes = [C.c_void_p]
+        L.ref_sgp_add.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        L.ref_sgp_predict.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.ref_sgp_cov.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        self.h = L.ref_sgp_new(kernel_string.encode(), float(sigma), float(jitter))
+        if not self.h:
+            raise RefError(L.ref_last_error().decode())
+        self.M = None
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().ref_sgp_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def add(self, X, Y, inducing=False):
+        X, Y = _f(X), _f(Y)
+        self.M = Y.shape[1]
+        _ck(lib().ref_sgp_add(self.h, _p(X), X.shape[0], X.shape[1], _p(Y), Y.shape[1], int(inducing)))
+        return self
+
+    def predict(self, x):
+        x = _f(x).ravel()
+        out = np.empty(self.M)
+        _ck(lib().ref_sgp_predict(self.h, _p(x), x.size, _p(out)))
+        return out
+
+    def cov(self, x, y):
+        x, y = _f(x).ravel(), _f(y).ravel()
+        out = C.c_double()
+        _ck(lib().ref_sgp_cov(self.h, _p(x), _p(y), x.size, C.byref(out)))
+        return out.value
+
+
 def pinv(A):
     """gpr::pinv (include/Prior.h:38-57)."""
     A = _f(np.atleast_2d(A))

@@ -366,4 +366,32 @@ int ref_gp_set_params(void* h, const double* p, int n) {
     });
 }
 
+
+// ---- SparseGaussianProcess (include/SparseGaussianProcess.h), regression part -----------------------------------
+void* ref_sgp_new(const char* ks, double sigma, double jitter) {
+    gpr::SparseGaussianProcess<double>* g = nullptr;
+    guard([&] {
+        std::string s(ks);
+        g = new gpr::SparseGaussianProcess<double>(gpr::KernelFactory<double>::GetKernel(s), jitter);
+        g->SetSigma(sigma);
+    });
+    return g;
+}
+void ref_sgp_free(void* h) { delete static_cast<gpr::SparseGaussianProcess<double>*>(h); }
+int ref_sgp_add(void* h, const double* X, long N, int d, const double* Y, int M, int inducing) {
+    return guard([&] {
+        auto* g = static_cast<gpr::SparseGaussianProcess<double>*>(h);
+        for (long i = 0; i < N; ++i) {
+            if (inducing) g->AddInducingSample(to_vec(X + i * d, d), to_vec(Y + i * M, M));
+            else g->AddSample(to_vec(X + i * d, d), to_vec(Y + i * M, M));
+        }
+    });
+}
+int ref_sgp_predict(void* h, const double* x, int d, double* out) {
+    return guard([&] { from_mat(static_cast<gpr::SparseGaussianProcess<double>*>(h)->Predict(to_vec(x, d)), out); });
+}
+int ref_sgp_cov(void* h, const double* x, const double* y, int d, double* out) {
+    return guard([&] { *out = (*static_cast<gpr::SparseGaussianProcess<double>*>(h))(to_vec(x, d), to_vec(y, d)); });
+}
+
 }  // extern "C"
