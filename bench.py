@@ -283,6 +283,10 @@ def run_gpu(args):
     if rank == 0 and not args.skip_pca:
         pca = run_pca(torch, gpr_b200, local_rank)
 
+    sparse = None
+    if rank == 0 and not args.skip_sparse:
+        sparse = run_sparse(torch, gpr_b200, local_rank)
+
     large = None
     if world > 1 and not args.skip_large:
         large = run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist)
@@ -336,6 +340,8 @@ def run_gpu(args):
             line["loglik"] = loglik
         if pca:
             line["pca_frame"] = pca
+        if sparse:
+            line["sparse"] = sparse
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
         if peaks:
@@ -584,6 +590,49 @@ def run_pca(torch, gpr_b200, local_rank, D=3 * 64 ** 3, n=256, nF=32, N=256, d=3
             "round_trip_rel_err": rt, "discarded_energy": tail}
 
 
+def run_sparse(torch, gpr_b200, local_rank, n=262144, m=4096, d=8):
+    """SURVEY 8(f) row 4: SparseGaussianProcess::PreComputeRegression (include/SparseGaussianProcess.h:274-312) at a
+    size whose dense kernel matrix (n^2 * 8 B = 550 GB) does not exist: cross-Gram Knm (n x m), S = K + sigma^-2 Kmn Knm
+    (n m^2 flop on the FP64 tensor path, lower triangle), two m x m Cholesky factorisations, alpha. Device-timed."""
+    rng = np.random.default_rng(SEED + 91)
+    X = rng.uniform(-1, 1, (n, d))
+    Y = np.sin(3.0 * X[:, :1]) + 0.5 * np.cos(2.0 * X[:, 1:2] + X[:, 2:3]) + 0.1 * rng.standard_normal((n, 1))
+    Xm = rng.uniform(-1, 1, (m, d))
+    dev = torch.device("cuda", local_rank)
+    h = gpr_b200.Handle(local_rank)
+    stream = torch.cuda.current_stream(dev)
+    h.set_stream(stream.cuda_stream)
+    ops, params = gpr_b200.KernelFactory.GetKernel(C3_KERNEL).lower()
+    h.set_kernel(ops, params)
+    h.set_train(X, Y, C3_SIGMA)
+    h._ck(h.lib.gprb200_sparse_set_inducing(h.h, Xm.ctypes.data, m, d, 1e-2))
+    h._ck(h.lib.gprb200_sparse_learn(h.h))          # warm-up
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = h.launch_count()
+    e0.record(stream)
+    for _ in range(3):
+        h._ck(h.lib.gprb200_sparse_learn(h.h))
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    launches = (h.launch_count() - l0) / 3
+    flops = 1.0 * n * m * m + 2.0 * m ** 3 / 3.0 + 2.0 * n * m   # S is symmetric: only its lower triangle is formed
+    Xs = rng.uniform(-1, 1, (256, d))
+    mean, var = np.empty((256, 1)), np.empty(256)
+    t0 = time.perf_counter()
+    h._ck(h.lib.gprb200_sparse_predict(h.h, Xs.ctypes.data, 256, mean.ctypes.data, var.ctypes.data))
+    pred_ms = (time.perf_counter() - t0) * 1e3
+    truth = np.sin(3.0 * Xs[:, 0]) + 0.5 * np.cos(2.0 * Xs[:, 1] + Xs[:, 2])
+    h.close()
+    return {"metric": "sparse_learn_ms", "value": ms, "n": n, "m": m, "d": d, "kernel": C3_KERNEL,
+            "tflops": flops / ms * 1e-9, "frac_of_fp64_peak": flops / ms * 1e-9 / FP64_PEAK_TFLOPS, "launches": launches,
+            "useful_flops": "n m^2 (lower triangle of S) + 2 m^3/3 (two Cholesky) + 2 n m (Kmn Y)",
+            "dense_equivalent": "K would be %.0f GB" % (8.0 * n * n * 1e-9),
+            "predict_256_with_variance_ms": pred_ms, "mean_abs_err_vs_truth": float(np.abs(mean[:, 0] - truth).mean()),
+            "variance_min": float(var.min())}
+
+
 def run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist):
     """C5: ONE model of N = 131072 samples factored across all ranks (block-cyclic Cholesky, NCCL panel broadcasts,
     gpr_b200/dist.py) + distributed solve. Strong scaling of a single large problem; device-timed, max over ranks."""
@@ -673,6 +722,7 @@ def main():
     ap.add_argument("--skip-large", action="store_true")
     ap.add_argument("--skip-loglik", action="store_true")
     ap.add_argument("--skip-pca", action="store_true")
+    ap.add_argument("--skip-sparse", action="store_true")
     ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")

@@ -165,6 +165,10 @@ protected:
     // grad (P), jacobian (M x P) may be null. Re-factorises with the current kernel parameters.
     void DeviceLogLikelihood(VectorType* value, VectorType* grad, MatrixType* jacobian) const;
 
+    // The gprb200_handle with kernel, samples and sigma in sync with the host state, WITHOUT learning the dense model
+    // (subclasses that factor something else on the same samples: SparseGaussianProcess.h).
+    void* SyncedDeviceHandle() const;
+
     DeterminantMode m_DeterminantMode;
     mutable unsigned m_CoreSize;  // what m_CoreMatrix.diagonalSize() is in the reference's state machine
 

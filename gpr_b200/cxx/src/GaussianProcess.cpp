@@ -282,6 +282,12 @@ TScalarType GaussianProcess<TScalarType>::GetCredibleInterval(const VectorType& 
 }
 
 template <class TScalarType>
+void* GaussianProcess<TScalarType>::SyncedDeviceHandle() const {
+    SyncModelToDevice();
+    return Device().h;
+}
+
+template <class TScalarType>
 void* GaussianProcess<TScalarType>::GetDeviceHandle() {
     Initialize();
     return Device().h;

@@ -40,6 +40,14 @@ def test_cxx_inference_program():
     assert rc == 0 and "[failed]" not in out, out[-4000:]
 
 
+def test_cxx_sparse_program():
+    """SparseGaussianProcess<T> over the device sparse path (tests/cxx/sparse_device_test.cpp)."""
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "sparse_device_test")
+    assert os.path.exists(exe), "tests/cxx/bin/sparse_device_test missing: run __graft_entry__.build()"
+    rc, out = _run(exe)
+    assert rc == 0 and "[failed]" not in out, out[-4000:]
+
+
 DROPIN = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "dropin", "*")))
 
 
