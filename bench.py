@@ -624,8 +624,28 @@ def run_sparse(torch, gpr_b200, local_rank, n=262144, m=4096, d=8):
     h._ck(h.lib.gprb200_sparse_predict(h.h, Xs.ctypes.data, 256, mean.ctypes.data, var.ctypes.data))
     pred_ms = (time.perf_counter() - t0) * 1e3
     truth = np.sin(3.0 * Xs[:, 0]) + 0.5 * np.cos(2.0 * Xs[:, 1] + Xs[:, 2])
+    # SparseGaussianLogLikelihood::GetValueAndParameterDerivatives (include/SparseLikelihood.h:287-409): one optimiser
+    # iteration = relearn + beta + two m x m inverses + Knm S^-1 (2 n m^2 flop) + the two fused dK contractions
+    P = len(params)
+    val, grad = np.empty(1), np.empty(P)
+    h._ck(h.lib.gprb200_sparse_loglik(h.h, 1, val.ctypes.data, grad.ctypes.data, None))   # warm-up
+    torch.cuda.synchronize()
+    l0 = h.launch_count()
+    e0.record(stream)
+    for _ in range(3):
+        h._ck(h.lib.gprb200_sparse_loglik(h.h, 1, val.ctypes.data, grad.ctypes.data, None))
+    e1.record(stream)
+    torch.cuda.synchronize()
+    lik_ms = e0.elapsed_time(e1) / 3
+    lik_launches = (h.launch_count() - l0) / 3
+    lik_flops = flops + 2.0 * n * m * m + 2.0 * (2.0 * m ** 3 / 3.0)
     h.close()
-    return {"metric": "sparse_learn_ms", "value": ms, "n": n, "m": m, "d": d, "kernel": C3_KERNEL,
+    loglik = {"ms_per_iteration": lik_ms, "launches": lik_launches, "P": P, "value": float(val[0]),
+              "grad": [float(g) for g in grad], "tflops": lik_flops / lik_ms * 1e-9,
+              "useful_flops": "learn + 2 n m^2 (Knm S^-1) + 2 x 2 m^3/3 (K^-1, S^-1); the dK contractions are ALU work on top",
+              "reference_equivalent": "P + 1 dense n x n matrices (%.0f GB each) and O(P n^3) = %.1e flop"
+                                      % (8.0 * n * n * 1e-9, 2.0 * P * 3 * float(n) ** 3)}
+    return {"metric": "sparse_learn_ms", "value": ms, "n": n, "m": m, "d": d, "kernel": C3_KERNEL, "loglik": loglik,
             "tflops": flops / ms * 1e-9, "frac_of_fp64_peak": flops / ms * 1e-9 / FP64_PEAK_TFLOPS, "launches": launches,
             "useful_flops": "n m^2 (lower triangle of S) + 2 m^3/3 (two Cholesky) + 2 n m (Kmn Y)",
             "dense_equivalent": "K would be %.0f GB" % (8.0 * n * n * 1e-9),

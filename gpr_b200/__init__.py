@@ -16,4 +16,4 @@ from .gp import (  # noqa: E402,F401
     FullPivotLU, JacobiSVD, BDCSVD, SelfAdjointEigenSolver)
 from .inference import GaussianProcessInference  # noqa: E402,F401
 from .pca import PCA  # noqa: E402,F401
-from .sparse import SparseGaussianProcess  # noqa: E402,F401
+from .sparse import SparseGaussianProcess, SparseGaussianLogLikelihood  # noqa: E402,F401

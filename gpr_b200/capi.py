@@ -61,6 +61,8 @@ _PROTOS = {
     "gprb200_sparse_set_jitter": (C.c_int, [C.c_void_p, C.c_double]),
     "gprb200_sparse_learn": (C.c_int, [C.c_void_p]),
     "gprb200_sparse_get_alpha": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gprb200_sparse_loglik": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gprb200_sparse_dgram_cross": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_sparse_predict": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "gprb200_sparse_cov": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_pca_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),

@@ -119,6 +119,11 @@ int dgram_build(Ctx* c, double* out /* (P*N) x N */, int64_t ldo);
 int check_finite(Ctx* c, const double* A, int64_t rows, int64_t cols, int64_t ld, bool lower_only, int* bad_host);
 // fused likelihood-gradient contraction: out[p] = sum_ij S_ij * dK_p(i,j), S symmetric N x N (lds)
 int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host /* P */);
+// the same between two point sets (sparse likelihood: n x m cross-Gram weights); Xa == Xb means symmetric
+int dgram_contract_xy(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, const double* W, int64_t ldw,
+                      double* out_host /* P */);
+int dgram_build_xy(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, double* out, int64_t ldo,
+                   int p_select);
 // dgemm.cu
 int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream = nullptr);
 int gemm_skinny(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream);  // skinny.cu, n <= 8
@@ -136,6 +141,9 @@ int inverse_from_factor(Ctx* c, const double* L, int64_t ldl, const double* invL
 int copy2d(Ctx* c, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t rows, int64_t cols);
 int fill2d(Ctx* c, double* dst, int64_t ldd, int64_t rows, int64_t cols, double v);
 int add_diag(Ctx* c, double* A, int64_t ld, int64_t n, double v);  // A(i,i) += v, i < n
+// dst = a A + b B element-wise on rows x cols (dst may alias A or B)
+int axpby2d(Ctx* c, double* dst, int64_t ldd, double a, const double* A, int64_t lda, double b, const double* B,
+            int64_t ldb, int64_t rows, int64_t cols);
 int set_identity(Ctx* c, double* dst, int64_t ldd, int64_t n);
 int symmetrize_from_lower(Ctx* c, double* A, int64_t ld, int64_t n);
 int zero_upper(Ctx* c, double* A, int64_t ld, int64_t n);

@@ -181,8 +181,9 @@ __global__ void __launch_bounds__(GTHREADS, DERIV ? 1 : 2) gram_kernel(GramArgs 
                     if (inb) {
                         kprog_deriv(P, g[ia][ib], dk);
                         if (a.S) {
-                            // S and dK are symmetric: off-diagonal tiles count twice
-                            const double w = a.S[i * a.lds + j] * (diag_tile ? 1.0 : 2.0);
+                            // symmetric S and dK: off-diagonal tiles count twice; a rectangular (cross) contraction
+                            // visits every tile once
+                            const double w = a.S[i * a.lds + j] * ((a.symmetric && !diag_tile) ? 2.0 : 1.0);
                             for (int p = 0; p < P.nparams; ++p) acc[p] = fma(w, dk[p], acc[p]);
                         } else if (a.p_select >= 0) {
                             a.out[i * a.ldo + j] = dk[a.p_select];
@@ -443,31 +444,44 @@ int kpair_values(Ctx* c, const double* Xa, const double* Xb, int64_t T, double* 
 int dgram_build_one(Ctx* c, double* out, int64_t ldo, int p_select);
 int dgram_build(Ctx* c, double* out, int64_t ldo) { return dgram_build_one(c, out, ldo, -1); }
 
-int dgram_build_one(Ctx* c, double* out, int64_t ldo, int p_select) {
+// dK_p between two point sets (Xa == Xb, Na == Nb: symmetric, mirrored). p_select < 0 stores the whole stack
+// ((P*Na) x Nb, block p at rows [p Na, (p+1) Na)), else parameter p only (Na x Nb).
+int dgram_build_xy(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, double* out, int64_t ldo,
+                   int p_select) {
     DevProg P;
     if (int r = lower_program(c->prog, &P, &c->err)) return r;
     if (p_select >= P.nparams) return fail(c, -2, "dgram: parameter index out of range");
+    const bool symmetric = (Xa == Xb && Na == Nb);
     GramArgs a{};
-    a.Xa = c->dX; a.Xb = c->dX; a.Na = c->N; a.Nb = c->N; a.d = c->d;
-    a.out = out; a.ldo = ldo; a.symmetric = 1; a.p_select = p_select;
-    const int64_t ta = (c->N + GT - 1) / GT;
-    a.tiles_b = (int)ta;
-    gram_kernel<true><<<(unsigned)sym_tiles(ta), GTHREADS, 0, c->stream>>>(a, P);
+    a.Xa = Xa; a.Xb = Xb; a.Na = Na; a.Nb = Nb; a.d = c->d;
+    a.out = out; a.ldo = ldo; a.symmetric = symmetric ? 1 : 0; a.p_select = p_select;
+    const int64_t ta = (Na + GT - 1) / GT, tb = (Nb + GT - 1) / GT;
+    a.tiles_b = (int)tb;
+    const int64_t grid = symmetric ? sym_tiles(ta) : ta * tb;
+    if (grid <= 0) return 0;
+    gram_kernel<true><<<(unsigned)grid, GTHREADS, 0, c->stream>>>(a, P);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     return 0;
 }
 
-int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host) {
+int dgram_build_one(Ctx* c, double* out, int64_t ldo, int p_select) {
+    return dgram_build_xy(c, c->dX, c->N, c->dX, c->N, out, ldo, p_select);
+}
+
+// out[p] = sum_ij W_ij dK_p(xa_i, xb_j); Xa == Xb (Na == Nb) takes W symmetric and visits the lower tiles only.
+int dgram_contract_xy(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, const double* W, int64_t ldw,
+                      double* out_host) {
     DevProg P;
     if (int r = lower_program(c->prog, &P, &c->err)) return r;
-    const int64_t ta = (c->N + GT - 1) / GT;
-    const int64_t grid = sym_tiles(ta);
+    const bool symmetric = (Xa == Xb && Na == Nb);
+    const int64_t ta = (Na + GT - 1) / GT, tb = (Nb + GT - 1) / GT;
+    const int64_t grid = symmetric ? sym_tiles(ta) : ta * tb;
     double* partial = nullptr;
     GP_CUDA(c, cudaMallocAsync(&partial, sizeof(double) * (grid + 1) * P.nparams, c->stream));
     GramArgs a{};
-    a.Xa = c->dX; a.Xb = c->dX; a.Na = c->N; a.Nb = c->N; a.d = c->d;
-    a.symmetric = 1; a.S = S; a.lds = lds; a.partial = partial; a.tiles_b = (int)ta; a.p_select = -1;
+    a.Xa = Xa; a.Xb = Xb; a.Na = Na; a.Nb = Nb; a.d = c->d;
+    a.symmetric = symmetric ? 1 : 0; a.S = W; a.lds = ldw; a.partial = partial; a.tiles_b = (int)tb; a.p_select = -1;
     gram_kernel<true><<<(unsigned)grid, GTHREADS, 0, c->stream>>>(a, P);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
@@ -479,6 +493,10 @@ int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host) {
     GP_CUDA(c, cudaStreamSynchronize(c->stream));
     GP_CUDA(c, cudaFreeAsync(partial, c->stream));
     return 0;
+}
+
+int dgram_contract(Ctx* c, const double* S, int64_t lds, double* out_host) {
+    return dgram_contract_xy(c, c->dX, c->N, c->dX, c->N, S, lds, out_host);
 }
 
 int check_finite(Ctx* c, const double* A, int64_t rows, int64_t cols, int64_t ld, bool lower_only, int* bad_host) {

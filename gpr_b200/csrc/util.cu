@@ -75,6 +75,22 @@ int copy2d(Ctx* c, double* dst, int64_t ldd, const double* src, int64_t lds, int
     GP_CUDA(c, cudaGetLastError());
     return 0;
 }
+__global__ void axpby2d_kernel(double* dst, int64_t ldd, double a, const double* A, int64_t lda, double b, const double* B,
+                               int64_t ldb, int64_t rows, int64_t cols) {
+    const int64_t total = rows * cols;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / cols, cc = e - r * cols;
+        dst[r * ldd + cc] = a * A[r * lda + cc] + b * B[r * ldb + cc];
+    }
+}
+int axpby2d(Ctx* c, double* dst, int64_t ldd, double a, const double* A, int64_t lda, double b, const double* B,
+            int64_t ldb, int64_t rows, int64_t cols) {
+    if (rows <= 0 || cols <= 0) return 0;
+    axpby2d_kernel<<<grid_for(rows * cols, 256), 256, 0, c->stream>>>(dst, ldd, a, A, lda, b, B, ldb, rows, cols);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    return 0;
+}
 int fill2d(Ctx* c, double* dst, int64_t ldd, int64_t rows, int64_t cols, double v) {
     if (rows <= 0 || cols <= 0) return 0;
     fill2d_kernel<<<grid_for(rows * cols, 256), 256, 0, c->stream>>>(dst, ldd, rows, cols, v, 0);

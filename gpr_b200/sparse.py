@@ -3,7 +3,7 @@ csrc/sparse.cu: same method names (AddInducingSample, ClearInducingSamples, SetJ
 operator()(x, y)). Dense samples come from the GaussianProcess base class (AddSample)."""
 import numpy as np
 
-from .capi import GprError, _f64, _ptr
+from .capi import GprError, _f64, _ptr, LOGLIK_REFERENCE_CLAMP
 from .gp import GaussianProcess
 
 
@@ -41,11 +41,8 @@ class SparseGaussianProcess(GaussianProcess):
         self.m_Jitter = float(jitter)
         self._sparse_dirty = True
 
-    def Initialize(self):
-        if not self.m_InducingSampleVectors:
-            raise GprError(-2, "SparseGaussianProcess::Initialize: no inducing samples defined during initialization")
-        if not self.m_SampleVectors:
-            raise GprError(-2, "SparseGaussianProcess::Initialize: no dense samples defined during initialization")
+    def _sync_sparse(self):
+        """kernel, dense samples, sigma and inducing points resident on the device; nothing is factored"""
         self._sync_kernel()
         self._sync_train()
         self._h.set_sigma(self.m_Sigma)
@@ -54,7 +51,14 @@ class SparseGaussianProcess(GaussianProcess):
             Xm = _f64(np.stack(self.m_InducingSampleVectors))
             h._ck(h.lib.gprb200_sparse_set_inducing(h.h, _ptr(Xm), Xm.shape[0], Xm.shape[1], self.m_Jitter))
             self._sparse_dirty = False
-        h._ck(h.lib.gprb200_sparse_learn(h.h))
+
+    def Initialize(self):
+        if not self.m_InducingSampleVectors:
+            raise GprError(-2, "SparseGaussianProcess::Initialize: no inducing samples defined during initialization")
+        if not self.m_SampleVectors:
+            raise GprError(-2, "SparseGaussianProcess::Initialize: no dense samples defined during initialization")
+        self._sync_sparse()
+        self._h._ck(self._h.lib.gprb200_sparse_learn(self._h.h))
 
     def RegressionVectors(self):
         self.Initialize()
@@ -86,3 +90,42 @@ class SparseGaussianProcess(GaussianProcess):
         out = np.empty(1)
         self._h._ck(self._h.lib.gprb200_sparse_cov(self._h.h, _ptr(x), _ptr(y), 1, _ptr(out)))
         return float(out[0])
+
+
+class SparseGaussianLogLikelihood:
+    """include/SparseLikelihood.h:111-551 over gprb200_sparse_loglik. `mode` selects the reference's long-double range
+    clamp of the complexity term (default) or the true -0.5 log det(sigma^2 I + Knm K^-1 Kmn)."""
+
+    def __init__(self, mode=LOGLIK_REFERENCE_CLAMP):
+        self.mode = mode
+
+    def ToString(self):
+        return "SparseGaussianLogLikelihood"
+
+    def _run(self, gp, want_value, want_grad, want_jac):
+        if not isinstance(gp, SparseGaussianProcess):
+            raise GprError(-2, "SparseGaussianLogLikelihood: cannot cast to SparseGaussianProcess")
+        if gp.GetNumberOfInducingSamples() == 0:
+            raise GprError(-2, "SparseLikelihood::GetValueAndParameterDerivative: there are no inducing samples specified")
+        gp._sync_sparse()
+        h = gp._h
+        M, P = gp.m_OutputDimension, gp.m_Kernel.GetNumberOfParameters()
+        v = np.empty(M) if want_value else None
+        g = np.empty(P) if want_grad else None
+        j = np.empty((M, P)) if want_jac else None
+        h._ck(h.lib.gprb200_sparse_loglik(h.h, int(self.mode), _ptr(v), _ptr(g), _ptr(j)))
+        return v, g, j
+
+    def __call__(self, gp):  # :152-217
+        return self._run(gp, True, False, False)[0]
+
+    def GetParameterDerivatives(self, gp):  # :219-285
+        return self._run(gp, False, True, False)[1]
+
+    def GetValueAndParameterDerivatives(self, gp):  # :287-409
+        v, g, _ = self._run(gp, True, True, False)
+        return v, g
+
+    def GetValueAndJacobian(self, gp):  # :411-535
+        v, _, j = self._run(gp, True, False, True)
+        return v, j

@@ -224,7 +224,7 @@ int gprb200_predict_reconstruct_dev(gprb200_handle h, gprb200_pca_handle p, cons
 
 /* ---- Sparse (inducing-point) GP (reference include/SparseGaussianProcess.h) ----
  * The dense samples are the handle's training set (set_train), the inducing points are added here. m <= n.
- * Regression part only: PreComputeRegression, Predict, operator()(x, y); the sparse likelihood is not provided. */
+ * PreComputeRegression, Predict, operator()(x, y), and the sparse log-likelihood (include/SparseLikelihood.h). */
 /* AddInducingSample x m (:61-76) + SetJitter (:118-121); Xm: m x d */
 int gprb200_sparse_set_inducing(gprb200_handle h, const double* Xm, int64_t m, int d, double jitter);
 int gprb200_sparse_set_jitter(gprb200_handle h, double jitter);
@@ -232,6 +232,20 @@ int gprb200_sparse_set_jitter(gprb200_handle h, double jitter);
  * alpha = sigma^-2 S^-1 Kmn Y (the value the reference's K^-1 (sigma^-2 K Sigma Kmn Y) reduces to). */
 int gprb200_sparse_learn(gprb200_handle h);
 int gprb200_sparse_get_alpha(gprb200_handle h, double* alpha); /* m x M regression vectors */
+/* SparseGaussianLogLikelihood (include/SparseLikelihood.h:152-535). Recomputes every matrix from the current kernel
+ * parameters, sigma and jitter, as the reference does on each call. mode as gprb200_loglik: REFERENCE_CLAMP follows
+ * EfficientDeterminant's long-double range and the clamps at :177-185 / :351-359, TRUE uses
+ * log det(sigma^2 I + Knm K^-1 Kmn) = n log sigma^2 - log det K + log det S from the two Cholesky factors.
+ *   value (M or NULL)      operator() (:152-217): -1/2 y_k^T C_inv y_k + cp + ct per output column k
+ *   grad  (P or NULL)      GetParameterDerivatives (:219-285); as the reference, an error unless M == 1
+ *   jac   (M x P or NULL)  GetValueAndJacobian (:411-535): row k = the gradient of the single-output problem on
+ *                          column k (the reference's own last line, :530, is only defined for M == P == 1)
+ * A NaN determinant is an error when only the value is asked for (:177-185 do not test for it) and clamps like an
+ * underflow otherwise (:351, :477). */
+int gprb200_sparse_loglik(gprb200_handle h, int mode, double* value, double* grad, double* jac);
+/* ComputeDerivativeKernelVectorMatrix (include/SparseGaussianProcess.h:237-264): the stack d k(x_i, z_j) / d theta_p,
+ * (P*n) x m row-major, block p at rows [p n, (p+1) n). The likelihood above never materialises it. */
+int gprb200_sparse_dgram_cross(gprb200_handle h, double* D_out);
 /* Predict (:84-90) for T points: mean T x M (may be NULL); var (may be NULL): operator()(x, x) per point */
 int gprb200_sparse_predict(gprb200_handle h, const double* Xs, int64_t T, double* mean, double* var);
 /* operator()(x, y) (:92-106) for T pairs: k(x,y) - Kx^T K^-1 Ky + Kx^T S^-1 Ky */

@@ -436,3 +436,97 @@ class SparseOracle:
         kx, ky = self.kx(x), self.kx(y)
         kxy = kernel_matrix(self.k, np.atleast_2d(x), np.atleast_2d(y))[0, 0]
         return kxy - kx @ self.Kinv @ ky + kx @ self.R @ ky
+
+
+# ---------------------------------------------------------------------------------------------------
+# SparseGaussianLogLikelihood: restatement of include/SparseLikelihood.h:111-551 with the
+# reference's explicit matrices (n x n C_inv, the stacked n x n grad(C) blocks), so small cases only.
+# ---------------------------------------------------------------------------------------------------
+def _ld_logabsdet(A):
+    """long-double determinant by LU (Eigen's PartialPivLU on cast<long double>()) as (sign, log|det|)."""
+    lu, piv, info = lapack.dgetrf(np.array(A.T, order="F"))
+    d = np.diag(lu)
+    sign = np.prod(np.sign(d)) * (-1.0) ** np.sum(piv != np.arange(len(piv)))
+    return sign, np.sum(np.log(np.abs(d).astype(np.longdouble)))
+
+
+class SparseLikOracle:
+    def __init__(self, kernel, X, Y, Xm, sigma, jitter):
+        self.k = parse_kernel(kernel) if isinstance(kernel, str) else kernel
+        self.X, self.Y, self.Xm = (np.asarray(a, dtype=np.float64) for a in (X, Y, Xm))
+        self.sigma, self.jitter = float(sigma), float(jitter)
+
+    def _core(self):
+        """ComputeCoreMatrices (include/SparseGaussianProcess.h:323-350) + EfficientInversion (:132-138)."""
+        n, m = len(self.X), len(self.Xm)
+        K = kernel_matrix(self.k, self.Xm, self.Xm) + self.jitter * np.eye(m)
+        K_inv = lu_invert(K)
+        Knm = kernel_matrix(self.k, self.X, self.Xm)
+        s2 = self.sigma * self.sigma
+        A_inv = np.full(n, 1.0 / s2)
+        Cm = lu_invert(K + (Knm.T * A_inv) @ Knm)                      # inv(B_inv + X' inv(A) X), B_inv = K
+        C_inv = np.diag(A_inv) - (A_inv[:, None] * Knm) @ Cm @ (Knm.T * A_inv)
+        return K, K_inv, Knm, s2, C_inv
+
+    def _cp(self, K, K_inv, Knm, s2, nan_to_min):
+        """EfficientDeterminant (:142-150) and the clamp (:177-185 for operator(), :351-359 otherwise)."""
+        n = len(self.X)
+        with np.errstate(over="ignore", under="ignore", invalid="ignore"):
+            sb, lb = _ld_logabsdet(K_inv)
+            det_B = sb * np.exp(lb)
+            if np.isinf(det_B):
+                det_B = LDBL_MAX
+            ss, ls = _ld_logabsdet(K + Knm.T @ Knm / s2)
+            prod = np.exp(np.longdouble(n) * np.log(np.longdouble(s2)))
+            det = det_B * prod * (ss * np.exp(ls))
+        if det <= LDBL_MIN or (nan_to_min and np.isnan(det)):
+            return -0.5 * np.log(LDBL_MIN)
+        if det > LDBL_MAX:
+            return -0.5 * np.log(LDBL_MAX)
+        return -0.5 * np.log(det)
+
+    def true_logdet(self):
+        """log det(sigma^2 I + Knm K^-1 Kmn) without the long-double range (what LOGLIK_TRUE uses)."""
+        K, K_inv, Knm, s2, _ = self._core()
+        return float(-_ld_logabsdet(K)[1] + len(self.X) * np.log(np.longdouble(s2)) + _ld_logabsdet(K + Knm.T @ Knm / s2)[1])
+
+    def value(self, clamp=True, nan_to_min=False):
+        K, K_inv, Knm, s2, C_inv = self._core()
+        n = len(self.X)
+        df = -0.5 * np.einsum("nk,nm,mk->k", self.Y, C_inv, self.Y)      # diagonal of -0.5 Y' C_inv Y (:170)
+        cp = self._cp(K, K_inv, Knm, s2, nan_to_min) if clamp else np.longdouble(-0.5 * self.true_logdet())
+        ct = -(n / 2.0) * math.log(2 * math.pi)                           # :198
+        v = (df.astype(np.longdouble) + (cp + np.longdouble(ct))).astype(np.float64)
+        if np.isnan(v.sum()):
+            raise FloatingPointError("SparseLikelihood::GetValueAndParameterDerivative: likelihood value is not a number.")
+        return v
+
+    def _grad_blocks(self):
+        K, K_inv, Knm, s2, C_inv = self._core()
+        n, m = Knm.shape
+        Kmm_d = kernel_derivative(self.k, self.Xm, self.Xm)               # ComputeDerivativeKernelMatrix (:389-397)
+        Knm_d = kernel_derivative(self.k, self.X, self.Xm)                # ComputeDerivativeKernelVectorMatrix (:237-264)
+        A = [Knm_d[p] @ K_inv @ Knm.T - Knm @ K_inv @ Kmm_d[p] @ K_inv @ Knm.T + Knm @ K_inv @ Knm_d[p].T
+             for p in range(len(Kmm_d))]                                  # :255-259
+        return C_inv, A
+
+    def grad(self):
+        """GetParameterDerivatives (:219-285); the reference throws unless M == 1 (:264)."""
+        if self.Y.shape[1] != 1:
+            raise ValueError("SparseLikelihood::GetParameterDerivatives: dimension missmatch in calculating derivative of data fit term")
+        C_inv, A = self._grad_blocks()
+        y = self.Y[:, 0]
+        dt = np.array([0.5 * y @ C_inv @ Ap @ C_inv @ y for Ap in A])     # :261-266
+        ct = np.array([-0.5 * np.trace(C_inv @ Ap) for Ap in A])          # :270-274
+        return dt + ct
+
+    def jacobian(self):
+        """GetValueAndJacobian (:411-535): J(i, p) = 0.5 y_i' C_inv A_p C_inv y_i - 0.5 tr(C_inv A_p). The reference's own
+        last line `df_jac.colwise() + cp_grad` (:530) adds a P-vector to the columns of an M x P matrix and its value
+        line (:440) assigns an M x M product to a vector, so the call is only defined for M == P == 1; the evident
+        intent is implemented: row i equals GetParameterDerivatives of the single-output problem on column i."""
+        C_inv, A = self._grad_blocks()
+        M, P = self.Y.shape[1], len(A)
+        df = np.array([[0.5 * self.Y[:, i] @ C_inv @ A[p] @ C_inv @ self.Y[:, i] for p in range(P)] for i in range(M)])
+        cp = np.array([-0.5 * np.trace(C_inv @ Ap) for Ap in A])
+        return df + cp[None, :]

@@ -281,6 +281,20 @@ class RefSparseGP:
         _ck(lib().ref_sgp_cov(self.h, _p(x), _p(y), x.size, C.byref(out)))
         return out.value
 
+    def set_params(self, params):
+        p = _f(params).ravel()
+        lib().ref_sgp_set_params.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        _ck(lib().ref_sgp_set_params(self.h, _p(p), p.size))
+
+    def loglik(self, what, P):
+        """SparseGaussianLogLikelihood (include/SparseLikelihood.h): what = 0 operator(), 1 GetParameterDerivatives,
+        2 GetValueAndParameterDerivatives, 3 GetValueAndJacobian. Returns (value[M], grad[P], jac[M x P]) with None for
+        what the call does not produce."""
+        lib().ref_sgp_loglik.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        value, grad, jac = np.empty(self.M), np.empty(P), np.empty((self.M, P))
+        _ck(lib().ref_sgp_loglik(self.h, int(what), _p(value), _p(grad), _p(jac)))
+        return (value if what in (0, 2, 3) else None, grad if what in (1, 2) else None, jac if what == 3 else None)
+
 
 def pinv(A):
     """gpr::pinv (include/Prior.h:38-57)."""

@@ -15,6 +15,7 @@
 #include "lib/GaussianProcess.cpp"  // -I/root/reference
 #include "include/GaussianProcessInference.h"  // the optimiser loop; boost stand-ins in eigen_lite
 #include "include/PCA.h"          // the reference's PCA, BDCSVD -> LAPACK dgesdd in eigen_lite
+#include "include/SparseLikelihood.h"  // SparseGaussianLogLikelihood
 
 // ---- LAPACK: the reference declares the un-prefixed Fortran symbols; scipy's OpenBLAS exports them
 //      with a scipy_ prefix (LP64).
@@ -392,6 +393,36 @@ int ref_sgp_predict(void* h, const double* x, int d, double* out) {
 }
 int ref_sgp_cov(void* h, const double* x, const double* y, int d, double* out) {
     return guard([&] { *out = (*static_cast<gpr::SparseGaussianProcess<double>*>(h))(to_vec(x, d), to_vec(y, d)); });
+}
+
+// ---- SparseGaussianLogLikelihood (include/SparseLikelihood.h:111-551) -------------------------------------------
+// what = 0: operator() -> value (M); 1: GetParameterDerivatives -> grad (P); 2: GetValueAndParameterDerivatives ->
+// value, grad; 3: GetValueAndJacobian -> value, jac (M x P row-major)
+int ref_sgp_loglik(void* h, int what, double* value, double* grad, double* jac) {
+    return guard([&] {
+        auto* g = static_cast<gpr::SparseGaussianProcess<double>*>(h);
+        std::shared_ptr<GP> gp(static_cast<GP*>(g), [](GP*) {});
+        gpr::SparseGaussianLogLikelihood<double> lik;
+        if (what == 0) {
+            from_mat(lik(gp), value);
+        } else if (what == 1) {
+            from_mat(lik.GetParameterDerivatives(gp), grad);
+        } else if (what == 2) {
+            auto vd = lik.GetValueAndParameterDerivatives(gp);
+            from_mat(vd.first, value);
+            from_mat(vd.second, grad);
+        } else {
+            auto vj = lik.GetValueAndJacobian(gp);
+            from_mat(vj.first, value);
+            from_mat(vj.second, jac);
+        }
+    });
+}
+int ref_sgp_set_params(void* h, const double* p, int n) {
+    return guard([&] {
+        std::vector<double> v(p, p + n);
+        static_cast<gpr::SparseGaussianProcess<double>*>(h)->GetKernel()->SetParameters(v);
+    });
 }
 
 }  // extern "C"

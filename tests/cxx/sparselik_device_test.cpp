@@ -1,0 +1,159 @@
+// GPU checks of gpr::SparseGaussianLogLikelihood<T> (gpr_b200/cxx/include/SparseLikelihood.h; needs a B200), with the
+// checks and thresholds of the reference's tests/SparseInferenceTest.cpp (Test1-Test4) on deterministic data:
+//   L1 EfficientInversion / EfficientDeterminant against the direct n x n inverse / determinant   (:97-132, 1e-7, 1e-10)
+//   L2 core matrix Knm K^-1 Kmn == dense kernel matrix when the inducing points are the samples   (:190-224, 1e-2)
+//      and GetKernelMatrixTrace == trace of the dense kernel matrix
+//   L3 GetParameterDerivatives against central differences of operator()                           (:295-335)
+//   L4 GaussianProcessInference::Optimize over the sparse likelihood increases it                  (:341-412)
+//   L5 error strings: dense GP passed in, no inducing samples, M != 1 gradient
+#include <cmath>
+#include <iostream>
+#include <memory>
+#include <string>
+
+#include "GaussianProcess.h"
+#include "GaussianProcessInference.h"
+#include "Kernel.h"
+#include "SparseGaussianProcess.h"
+#include "SparseLikelihood.h"
+
+using namespace gpr;
+
+static int failures = 0;
+#define EXPECT(cond, what)                                                   \
+    do {                                                                     \
+        if (!(cond)) {                                                       \
+            ++failures;                                                      \
+            std::cout << "[failed] " << what << " (" #cond ")" << std::endl; \
+        } else {                                                             \
+            std::cout << "[passed] " << what << std::endl;                   \
+        }                                                                    \
+    } while (0)
+
+typedef GaussianProcess<double> GP;
+typedef SparseGaussianProcess<double> SGP;
+typedef SparseGaussianLogLikelihood<double> SLik;
+typedef GP::VectorType Vec;
+typedef GP::MatrixType Mat;
+typedef GP::DiagMatrixType Diag;
+
+static Vec V1(double v) {
+    Vec x(1);
+    x[0] = v;
+    return x;
+}
+static double f(double x) { return std::sin(x) + 0.3 * std::cos(2.5 * x); }
+// deterministic stand-in for the reference's normal noise
+static double wobble(unsigned i) { return 0.05 * std::sin(12.9898 * (i + 1)) * std::cos(78.233 * (i + 1)); }
+
+static std::shared_ptr<SGP> Make(double sigma, double scale, unsigned n, unsigned stride, double noise, double jitter) {
+    Kernel<double>::Pointer k(new GaussianKernel<double>(sigma, scale));
+    std::shared_ptr<SGP> g(new SGP(k, jitter));
+    g->SetSigma(noise);
+    for (unsigned i = 0; i < n; ++i) {
+        const double x = -4.0 + 8.0 * i / n;
+        g->AddSample(V1(x), V1(f(x) + wobble(i)));
+        if (i % stride == 0) g->AddInducingSample(V1(x), V1(f(x)));
+    }
+    return g;
+}
+
+int main() {
+    try {
+        std::shared_ptr<SLik> lik(new SLik());
+        {   // L1
+            std::shared_ptr<SGP> g = Make(1.2, 1.0, 40, 4, 0.5, 0.01);
+            Mat K, K_inv, Knm, D;
+            Diag I_sigma;
+            lik->GetCoreMatrices(g, K, K_inv, Knm, I_sigma);
+            EXPECT(K.rows() == 10 && Knm.rows() == 40 && Knm.cols() == 10 && I_sigma.rows() == 40, "L1 GetCoreMatrices shapes");
+            lik->EfficientInversion(g, D, I_sigma, K_inv, K, Knm);
+            const Mat full = Mat(I_sigma) + Knm * K_inv * Knm.adjoint();
+            const Mat T = full.inverse();
+            EXPECT((D - T).norm() < 1e-7, "L1 EfficientInversion == direct inverse");
+            const double det = (double)lik->EfficientDeterminant(I_sigma, K_inv, K, Knm);
+            const double direct = full.determinant();
+            EXPECT(std::fabs(det - direct) < 1e-10 * std::fabs(direct) + 1e-10, "L1 EfficientDeterminant == direct determinant");
+        }
+        {   // L2
+            std::shared_ptr<SGP> g = Make(1.2, 1.0, 60, 1, 0.1, 0.001);
+            Mat K, K_inv, Kmn, C, M;
+            Diag I_sigma;
+            lik->GetCoreMatrices(g, K, K_inv, Kmn, I_sigma);
+            lik->GetCoreMatrix(g, C, K_inv, Kmn);
+            g->ComputeDenseKernelMatrix(M);
+            EXPECT((C - M).norm() < 1e-2, "L2 core matrix == dense kernel matrix at m == n");
+            EXPECT(std::fabs(M.trace() - lik->GetKernelMatrixTrace(g)) < 1e-12 * 60, "L2 kernel matrix trace");
+        }
+        {   // L3
+            const double sigma = 1.3, scale = 0.9, h = 1e-4;
+            std::shared_ptr<SGP> g = Make(sigma, scale, 120, 3, 0.2, 0.05);
+            g->SetDeterminantMode(GP::TrueLogDeterminant);
+            const Vec D = lik->GetParameterDerivatives(g);
+            auto val = [&](double s, double c) {
+                g->SetKernel(Kernel<double>::Pointer(new GaussianKernel<double>(s, c)));
+                return (*lik)(g)[0];
+            };
+            const double d0 = (val(sigma + h / 2, scale) - val(sigma - h / 2, scale)) / h;
+            const double d1 = (val(sigma, scale + h / 2) - val(sigma, scale - h / 2)) / h;
+            EXPECT(std::fabs(D[0] - d0) < 1e-5 * (1 + std::fabs(d0)) && std::fabs(D[1] - d1) < 1e-5 * (1 + std::fabs(d1)),
+                   "L3 GetParameterDerivatives == central differences of operator()");
+            g->SetKernel(Kernel<double>::Pointer(new GaussianKernel<double>(sigma, scale)));
+            auto vd = lik->GetValueAndParameterDerivatives(g);
+            auto vj = lik->GetValueAndJacobian(g);
+            EXPECT(std::fabs(vd.second[0] - D[0]) < 1e-9 * (1 + std::fabs(D[0])) && std::fabs(vj.second(0, 1) - D[1]) < 1e-9 * (1 + std::fabs(D[1])) &&
+                       vd.first[0] == vj.first[0],
+                   "L3 value/gradient/Jacobian calls agree");
+            const double before = (*lik)(g)[0];
+            const double pred = g->Predict(V1(0.3))[0];
+            EXPECT(std::isfinite(before) && std::fabs(pred - f(0.3)) < 0.1, "L3 Predict after the likelihood uses the current parameters");
+        }
+        {   // L4
+            std::shared_ptr<SGP> g(new SGP(Kernel<double>::Pointer(new GaussianExpKernel<double>(1.0, 1.0)), 0.11));
+            g->SetSigma(0.1);
+            g->SetDeterminantMode(GP::TrueLogDeterminant);
+            const unsigned n = 300, m = 50;
+            auto ft = [](double x) { return (0.5 * std::sin(x + 10 * x) + std::sin(4 * x)) * x * x; };
+            for (unsigned i = 0; i < n; ++i) {
+                const double x = -5 + i * 15.0 / n;
+                g->AddSample(V1(x), V1(ft(x) + 2 * wobble(i)));
+            }
+            for (unsigned i = 0; i < m; ++i) {
+                const double x = -5 + (i * 6) * 15.0 / n;
+                g->AddInducingSample(V1(x), V1(ft(x)));
+            }
+            const double before = (*lik)(g)[0];
+            typedef GaussianProcessInference<double> Inference;
+            Inference::Pointer gpi(new Inference(lik, g, 1e-1, 30));
+            gpi->Optimize(false, false);
+            const double after = (*lik)(g)[0];
+            std::cout << "    sparse log-likelihood " << before << " -> " << after << std::endl;
+            EXPECT(std::isfinite(after) && after > before, "L4 Optimize over the sparse likelihood increases it");
+        }
+        {   // L5
+            bool t1 = false, t2 = false, t3 = false;
+            GP::Pointer dense(new GP(Kernel<double>::Pointer(new GaussianKernel<double>(1.0, 1.0))));
+            dense->AddSample(V1(0.0), V1(1.0));
+            try { (*lik)(dense); } catch (std::string& s) { t1 = s.find("cannot cast to SparseGaussianProcess") != std::string::npos; }
+            std::shared_ptr<SGP> none(new SGP(Kernel<double>::Pointer(new GaussianKernel<double>(1.0, 1.0)), 0.1));
+            none->AddSample(V1(0.0), V1(1.0));
+            try { (*lik)(none); } catch (std::string& s) { t2 = s.find("there are no inducing samples specified") != std::string::npos; }
+            std::shared_ptr<SGP> two(new SGP(Kernel<double>::Pointer(new GaussianKernel<double>(1.0, 1.0)), 0.1));
+            two->SetSigma(0.3);
+            Vec y2(2);
+            for (unsigned i = 0; i < 20; ++i) {
+                y2[0] = f(0.2 * i); y2[1] = f(0.3 * i);
+                two->AddSample(V1(0.2 * i), y2);
+                if (i % 4 == 0) two->AddInducingSample(V1(0.2 * i), y2);
+            }
+            try { lik->GetParameterDerivatives(two); } catch (std::string& s) { t3 = s.find("dimension missmatch") != std::string::npos; }
+            auto vj = lik->GetValueAndJacobian(two);
+            EXPECT(t1 && t2 && t3 && vj.second.rows() == 2 && vj.second.cols() == 2, "L5 error strings and the M = 2 Jacobian shape");
+        }
+    } catch (std::string& s) {
+        std::cout << "[failed] exception: " << s << std::endl;
+        return 1;
+    }
+    std::cout << (failures ? "FAILED" : "ALL PASSED") << std::endl;
+    return failures ? 1 : 0;
+}

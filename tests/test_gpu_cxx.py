@@ -48,6 +48,15 @@ def test_cxx_sparse_program():
     assert rc == 0 and "[failed]" not in out, out[-4000:]
 
 
+def test_cxx_sparse_likelihood_program():
+    """SparseGaussianLogLikelihood<T> (tests/cxx/sparselik_device_test.cpp): the checks of the reference's
+    tests/SparseInferenceTest.cpp Test1-Test4 on deterministic data."""
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "sparselik_device_test")
+    assert os.path.exists(exe), "tests/cxx/bin/sparselik_device_test missing: run __graft_entry__.build()"
+    rc, out = _run(exe)
+    assert rc == 0 and "[failed]" not in out, out[-4000:]
+
+
 DROPIN = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "dropin", "*")))
 
 
