@@ -71,6 +71,7 @@ struct Ctx {
     double logdet = 0.0;
 
     int64_t opt_gram_lower_only = 1;
+    int64_t opt_gram_terms = 2;   // value Gram: 2 row-group kernel (gram_rows_kernel), 1 per-tile term form, 0 interpreter
     int64_t opt_nbo = 0;          // outer (trailing-update) block of the two-level Cholesky; 0 = auto (512 / 1024)
     int64_t opt_chol_left = 0;    // left-looking outer loop (long-K column updates): measured slower, see potrf.cu
     int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs

@@ -238,6 +238,556 @@ __global__ void __launch_bounds__(GTHREADS, DERIV ? 1 : 2) gram_kernel(GramArgs 
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// exp(x) for x <= 0 (every exponential of the kernel family has a non-positive argument: -r^2/(2 sigma^2),
+// -sum sin^2/(2 sigma^2)). Branch-free: n = rint(x log2 e) by the magic-constant trick, r = x - n ln2 (two-term ln2),
+// degree-13 Taylor polynomial on |r| <= ln2/2 (truncation 4e-18 relative), 2^n folded into the exponent field.
+// Below -708 the result is 0 (the true value is < 3.3e-308; no denormal path). Relative error <= 2 ulp.
+__device__ __forceinline__ double exp_nonpos(double x) {
+    const double MAGIC = 6755399441055744.0;   // 1.5 * 2^52
+    const double t = fma(x, 1.4426950408889634074, MAGIC);
+    const int n = __double2loint(t);
+    const double nd = t - MAGIC;
+    double r = fma(nd, -6.93147180559945286227e-01, x);
+    r = fma(nd, -2.31904681384629955842e-17, r);
+    double p = 1.6059043836821613e-10;                 // 1/13!
+    p = fma(p, r, 2.08767569878680990e-09);            // 1/12!
+    p = fma(p, r, 2.50521083854417188e-08);            // 1/11!
+    p = fma(p, r, 2.75573192239858907e-07);            // 1/10!
+    p = fma(p, r, 2.75573192239858907e-06);            // 1/9!
+    p = fma(p, r, 2.48015873015873016e-05);            // 1/8!
+    p = fma(p, r, 1.98412698412698413e-04);            // 1/7!
+    p = fma(p, r, 1.38888888888888889e-03);            // 1/6!
+    p = fma(p, r, 8.33333333333333333e-03);            // 1/5!
+    p = fma(p, r, 4.16666666666666667e-02);            // 1/4!
+    p = fma(p, r, 1.66666666666666667e-01);            // 1/3!
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const double res = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+    return (x < -708.0) ? 0.0 : res;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Value Gram in term form (DevProg::nterms > 0): the default K1 kernel.
+//   * a thread owns 4 consecutive rows x 2 consecutive columns per pass (two passes over the 64 tile columns), so the
+//     per-dimension operands come from shared memory as 16-byte loads (3 LDS per 8 pairs) and K leaves as 16-byte stores;
+//   * the kernel program is walked ONCE per thread and pass, term by term and leaf by leaf, each leaf evaluated for the
+//     8 pairs in a row with its opcode branch outside the loop - no per-entry interpreter, no evaluation stack;
+//   * the points and the trig features of ALL PERIODIC leaves are staged together, once per CTA when d <= GDC
+//     (one barrier per tile instead of two per pass and leaf);
+//   * NPER (number of PERIODIC leaves) is a template parameter so the trig-feature accumulators are exactly sized.
+// lib/GaussianProcess.cpp:384-402 (+ :375-381 for the diagonal), ComputeKernelVectorInternal :684-693 for Xa != Xb.
+template <int NPER>
+__global__ void __launch_bounds__(GTHREADS, 2) gram_value_kernel(GramArgs a, DevProg P, int vec_ok) {
+    constexpr int NS = NPER > 0 ? NPER : 1;
+    extern __shared__ __align__(16) unsigned char gv_smem[];
+    typedef double Row[GT];
+    typedef double2 Row2[GT];
+    Row* xa = reinterpret_cast<Row*>(gv_smem);                                   // [GDC][GT]
+    Row* xb = xa + GDC;                                                          // [GDC][GT]
+    Row2* fa = reinterpret_cast<Row2*>(xb + GDC);                                // [NPER][GDC][GT] (cos, sin)(2 b x_d)
+    Row2* fb = fa + NPER * GDC;                                                  // [NPER][GDC][GT]
+    double (*tr)[GT / 2 + 1] = reinterpret_cast<double (*)[GT / 2 + 1]>(fb + NPER * GDC);   // [GT][GT/2+1] mirror staging
+
+    int ti, tj;
+    tile_from_linear(blockIdx.x, a.symmetric, a.tiles_b, ti, tj);
+    const int64_t i0 = (int64_t)ti * GT, j0 = (int64_t)tj * GT;
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const bool diag_tile = a.symmetric && (ti == tj);
+    const bool mirror = a.symmetric && !a.lower_only && !diag_tile;
+    const bool one_chunk = a.d <= GDC;
+    int bad = 0;
+
+    auto stage = [&](int d0, int dc) {
+        for (int e = tid; e < GT * GDC; e += GTHREADS) {
+            const int r = e & (GT - 1), dd = e / GT;
+            const bool ina = (dd < dc) && (i0 + r < a.Na), inb = (dd < dc) && (j0 + r < a.Nb);
+            xa[dd][r] = ina ? a.Xa[(i0 + r) * a.d + d0 + dd] : 0.0;
+            xb[dd][r] = inb ? a.Xb[(j0 + r) * a.d + d0 + dd] : 0.0;
+#pragma unroll
+            for (int q = 0; q < NPER; ++q) {
+                fa[q * GDC + dd][r] = ina ? *reinterpret_cast<const double2*>(a.Fa + ((((i0 + r) * NPER + q) * a.d) + d0 + dd) * 2)
+                                          : make_double2(1.0, 0.0);
+                fb[q * GDC + dd][r] = inb ? *reinterpret_cast<const double2*>(a.Fb + ((((j0 + r) * NPER + q) * a.d) + d0 + dd) * 2)
+                                          : make_double2(1.0, 0.0);
+            }
+        }
+    };
+    if (one_chunk) {
+        stage(0, a.d);
+        __syncthreads();
+    }
+
+    for (int pass = 0; pass < 2; ++pass) {
+        const int lj0 = pass * (GT / 2) + 2 * tx;   // first of this thread's two tile columns
+        double r2[4][2], S[NS][4][2];
+#pragma unroll
+        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+            for (int ib = 0; ib < 2; ++ib) {
+                r2[ia][ib] = 0.0;
+#pragma unroll
+                for (int q = 0; q < NS; ++q) S[q][ia][ib] = 0.0;
+            }
+
+        for (int d0 = 0; d0 < a.d; d0 += GDC) {
+            const int dc = min(GDC, a.d - d0);
+            if (!one_chunk) {
+                __syncthreads();
+                stage(d0, dc);
+                __syncthreads();
+            }
+            for (int dd = 0; dd < dc; ++dd) {
+                const double2 a01 = *reinterpret_cast<const double2*>(&xa[dd][4 * ty]);
+                const double2 a23 = *reinterpret_cast<const double2*>(&xa[dd][4 * ty + 2]);
+                const double2 b01 = *reinterpret_cast<const double2*>(&xb[dd][lj0]);
+                const double va[4] = {a01.x, a01.y, a23.x, a23.y};
+                const double vb[2] = {b01.x, b01.y};
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) {
+                        const double dx = va[ia] - vb[ib];
+                        r2[ia][ib] = fma(dx, dx, r2[ia][ib]);
+                    }
+            }
+            // sum_d sin^2(b (x_d - y_d)) = d/2 - 1/2 sum_d [cos(2b x_d) cos(2b y_d) + sin(2b x_d) sin(2b y_d)]
+            // with the per-point features of periodic_features_kernel: a 2 dc-long dot product per pair
+#pragma unroll
+            for (int q = 0; q < NPER; ++q) {
+                for (int dd = 0; dd < dc; ++dd) {
+                    double2 ca[4], cb[2];
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia) ca[ia] = fa[q * GDC + dd][4 * ty + ia];
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) cb[ib] = fb[q * GDC + dd][lj0 + ib];
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                        for (int ib = 0; ib < 2; ++ib)
+                            S[q][ia][ib] = fma(ca[ia].x, cb[ib].x, fma(ca[ia].y, cb[ib].y, S[q][ia][ib]));
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < NPER; ++q)
+#pragma unroll
+            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib) S[q][ia][ib] = fmax(0.0, 0.5 * ((double)a.d - S[q][ia][ib]));
+
+        // k = sum_t prod_l leaf_l, leaf by leaf over the 8 pairs
+        double acc[4][2];
+#pragma unroll
+        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+            for (int ib = 0; ib < 2; ++ib) acc[ia][ib] = 0.0;
+        for (int t = 0; t < P.nterms; ++t) {
+            double prod[4][2];
+            const int k0 = P.term_start[t], k1 = P.term_start[t + 1];
+            for (int k = k0; k < k1; ++k) {
+                const int node = P.term_leaf[k];
+                const int op = P.op[node];
+                const double c0 = P.cst[node][0], c1 = P.cst[node][1], c2 = P.cst[node][2];
+                double v[4][2];
+                switch (op) {
+                    case GPRB200_K_GAUSSIAN:
+                    case GPRB200_K_GAUSSIAN_EXP:
+#pragma unroll
+                        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                            for (int ib = 0; ib < 2; ++ib) v[ia][ib] = c0 * exp_nonpos(c1 * r2[ia][ib]);
+                        break;
+                    case GPRB200_K_WHITE:
+#pragma unroll
+                        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                            for (int ib = 0; ib < 2; ++ib) v[ia][ib] = (r2[ia][ib] == 0.0) ? c0 : 0.0;
+                        break;
+                    case GPRB200_K_RQ:
+#pragma unroll
+                        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                            for (int ib = 0; ib < 2; ++ib) v[ia][ib] = c0 * pow(fma(c1, r2[ia][ib], 1.0), c2);
+                        break;
+                    default: {  // PERIODIC
+                        const int slot = P.perslot[node];
+#pragma unroll
+                        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                            for (int ib = 0; ib < 2; ++ib) v[ia][ib] = 0.0;
+#pragma unroll
+                        for (int q = 0; q < NS; ++q)
+                            if (slot == q) {   // uniform
+#pragma unroll
+                                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                                    for (int ib = 0; ib < 2; ++ib) v[ia][ib] = c0 * exp_nonpos(c1 * S[q][ia][ib]);
+                            }
+                    } break;
+                }
+                if (k == k0) {
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                        for (int ib = 0; ib < 2; ++ib) prod[ia][ib] = v[ia][ib];
+                } else {
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                        for (int ib = 0; ib < 2; ++ib) prod[ia][ib] *= v[ia][ib];
+                }
+            }
+#pragma unroll
+            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib) acc[ia][ib] += prod[ia][ib];
+        }
+
+#pragma unroll
+        for (int ia = 0; ia < 4; ++ia) {
+            const int li = 4 * ty + ia;
+            const int64_t i = i0 + li, j = j0 + lj0;
+            if (a.symmetric) {
+                if (i == j) acc[ia][0] += a.diag_add;
+                if (i == j + 1) acc[ia][1] += a.diag_add;
+            }
+            const bool in0 = (i < a.Na) && (j < a.Nb), in1 = (i < a.Na) && (j + 1 < a.Nb);
+            if ((in0 && !isfinite(acc[ia][0])) || (in1 && !isfinite(acc[ia][1]))) bad = 1;
+            const bool tri = a.symmetric && a.lower_only && diag_tile;   // keep only j <= i
+            if (vec_ok && in1 && !(tri && j + 1 > i)) {
+                *reinterpret_cast<double2*>(&a.out[i * a.ldo + j]) = make_double2(acc[ia][0], acc[ia][1]);
+            } else {
+                if (in0 && !(tri && j > i)) a.out[i * a.ldo + j] = acc[ia][0];
+                if (in1 && !(tri && j + 1 > i)) a.out[i * a.ldo + j + 1] = acc[ia][1];
+            }
+            if (mirror) {
+                tr[li][2 * tx] = acc[ia][0];
+                tr[li][2 * tx + 1] = acc[ia][1];
+            }
+        }
+        if (mirror) {
+            __syncthreads();
+            // out(j0 + pass 32 + r, i0 + c) = tile(c, r): consecutive threads walk the contiguous direction
+            for (int e = tid; e < GT * (GT / 2); e += GTHREADS) {
+                const int r = e / GT, cc = e - r * GT;
+                const int64_t j = j0 + pass * (GT / 2) + r, i = i0 + cc;
+                if (j < a.Nb && i < a.Na) a.out[j * a.ldo + i] = tr[cc][r];
+            }
+            __syncthreads();
+        }
+    }
+    // finite check of ComputeKernelMatrixInternal (lib/GaussianProcess.cpp:399), fused into the build
+    if (a.nonfinite && __syncthreads_or(bad) && tid == 0) atomicAdd(a.nonfinite, 1);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Value Gram, row-group form: the kernel gram_build launches whenever all d dimensions of a 64-point tile fit in
+// shared memory (always for the BASELINE configs). On top of gram_value_kernel:
+//   * a CTA owns tile row ti and GROUP consecutive tile columns: the row side (points + trig features) is staged once,
+//     the column side is double-buffered with cp.async - the next tile's points land while this tile is computed, so no
+//     global-memory latency is exposed after the first tile;
+//   * FP64 DFMA has a ~40-cycle dependent latency on sm_100 (tools/fp64_probe.cu: one warp with 16 independent chains
+//     reaches 79 % of the pipe), so the exponentials of a thread's 8 pairs are evaluated in lock step (8 independent
+//     Horner chains per warp, 32 per scheduler) instead of one call after another;
+//   * single-leaf terms accumulate straight into the result (no product registers live).
+template <int MODE>   // 0: dst = v, 1: dst *= v, 2: dst += v   with v = c0 exp(c1 src), src >= 0 >= c1
+__device__ __forceinline__ void exp_leaf8(const double (&src)[4][2], double c0, double c1, double (&dst)[4][2]) {
+    const double MAGIC = 6755399441055744.0;
+    double r[4][2], p[4][2];
+    int n[4][2];
+#pragma unroll
+    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+        for (int ib = 0; ib < 2; ++ib) {
+            const double x = c1 * src[ia][ib];
+            const double t = fma(x, 1.4426950408889634074, MAGIC);
+            n[ia][ib] = __double2loint(t);
+            const double nd = t - MAGIC;
+            r[ia][ib] = fma(nd, -2.31904681384629955842e-17, fma(nd, -6.93147180559945286227e-01, x));
+            p[ia][ib] = fma(1.6059043836821613e-10, r[ia][ib], 2.08767569878680990e-09);
+        }
+    const double cf[12] = {2.50521083854417188e-08, 2.75573192239858907e-07, 2.75573192239858907e-06,
+                           2.48015873015873016e-05, 1.98412698412698413e-04, 1.38888888888888889e-03,
+                           8.33333333333333333e-03, 4.16666666666666667e-02, 1.66666666666666667e-01, 0.5, 1.0, 1.0};
+#pragma unroll
+    for (int k = 0; k < 12; ++k)
+#pragma unroll
+        for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+            for (int ib = 0; ib < 2; ++ib) p[ia][ib] = fma(p[ia][ib], r[ia][ib], cf[k]);
+#pragma unroll
+    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+        for (int ib = 0; ib < 2; ++ib) {
+            double v = __hiloint2double(__double2hiint(p[ia][ib]) + (n[ia][ib] << 20), __double2loint(p[ia][ib]));
+            v = (n[ia][ib] < -1021) ? 0.0 : v;     // below 2^-1022: no denormal path
+            if (MODE == 0) dst[ia][ib] = c0 * v;
+            else if (MODE == 1) dst[ia][ib] *= c0 * v;
+            else dst[ia][ib] = fma(c0, v, dst[ia][ib]);
+        }
+}
+
+template <int MODE, int NS>
+__device__ __forceinline__ void leaf8(const DevProg& P, int node, const double (&r2)[4][2], const double (&S)[NS][4][2],
+                                      double (&dst)[4][2]) {
+    const int op = P.op[node];
+    const double c0 = P.cst[node][0], c1 = P.cst[node][1];
+    switch (op) {
+        case GPRB200_K_GAUSSIAN:
+        case GPRB200_K_GAUSSIAN_EXP:
+            exp_leaf8<MODE>(r2, c0, c1, dst);
+            break;
+        case GPRB200_K_PERIODIC: {
+            const int slot = P.perslot[node];
+#pragma unroll
+            for (int q = 0; q < NS; ++q)
+                if (slot == q) exp_leaf8<MODE>(S[q], c0, c1, dst);   // uniform branch, static register indexing
+        } break;
+        default: {
+            const double c2 = P.cst[node][2];
+#pragma unroll
+            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib) {
+                    const double v = (op == GPRB200_K_WHITE) ? ((r2[ia][ib] == 0.0) ? c0 : 0.0)
+                                                             : c0 * pow(fma(c1, r2[ia][ib], 1.0), c2);   // RQ
+                    if (MODE == 0) dst[ia][ib] = v;
+                    else if (MODE == 1) dst[ia][ib] *= v;
+                    else dst[ia][ib] += v;
+                }
+        } break;
+    }
+}
+
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+
+constexpr int GGROUP = 4;   // tile columns per CTA
+
+template <int NPER>
+__global__ void __launch_bounds__(GTHREADS, 2) gram_rows_kernel(GramArgs a, DevProg P, int vec_ok, int use_tr) {
+    constexpr int NS = NPER > 0 ? NPER : 1;
+    extern __shared__ __align__(16) unsigned char gv_smem[];
+    const int d = a.d;
+    // layout: xa [d][GT] | xb [2][d][GT] | fa [NPER][d][GT] double2 | fb [2][NPER][d][GT] double2 | tr [GT][GT/2+1]
+    double* xa = reinterpret_cast<double*>(gv_smem);
+    double* xb = xa + d * GT;
+    double2* fa = reinterpret_cast<double2*>(xb + 2 * d * GT);
+    double2* fb = fa + NPER * d * GT;
+    double (*tr)[GT / 2 + 1] = reinterpret_cast<double (*)[GT / 2 + 1]>(fb + 2 * NPER * d * GT);
+
+    const int ti = blockIdx.y;
+    const int tj_begin = blockIdx.x * GGROUP;
+    int tj_end = min(tj_begin + GGROUP, a.tiles_b);
+    if (a.symmetric) tj_end = min(tj_end, ti + 1);
+    if (tj_begin >= tj_end) return;
+    const int64_t i0 = (int64_t)ti * GT;
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    int bad = 0, expmax = 0;
+
+    // out-of-range points are staged as zeros / (1, 0): their pairs are computed and never stored
+    auto stage_side = [&](const double* X, const double* F, int64_t row0, int64_t nrows, double* xs, double2* fs) {
+        for (int e = tid; e < GT * d; e += GTHREADS) {
+            const int r = e & (GT - 1), dd = e / GT;
+            if (row0 + r < nrows) {
+                cp_async8(&xs[dd * GT + r], X + (row0 + r) * d + dd);
+#pragma unroll
+                for (int q = 0; q < NPER; ++q)
+                    cp_async16(&fs[(q * d + dd) * GT + r], F + (((row0 + r) * NPER + q) * d + dd) * 2);
+            } else {
+                xs[dd * GT + r] = 0.0;
+#pragma unroll
+                for (int q = 0; q < NPER; ++q) fs[(q * d + dd) * GT + r] = make_double2(1.0, 0.0);
+            }
+        }
+    };
+    stage_side(a.Xa, a.Fa, i0, a.Na, xa, fa);
+    stage_side(a.Xb, a.Fb, (int64_t)tj_begin * GT, a.Nb, xb, fb);
+    asm volatile("cp.async.commit_group;\n" ::);
+
+    for (int tj = tj_begin; tj < tj_end; ++tj) {
+        const int buf = (tj - tj_begin) & 1;
+        const double* xbc = xb + buf * d * GT;
+        const double2* fbc = fb + buf * NPER * d * GT;
+        if (tj + 1 < tj_end) {
+            stage_side(a.Xb, a.Fb, (int64_t)(tj + 1) * GT, a.Nb, xb + (buf ^ 1) * d * GT, fb + (buf ^ 1) * NPER * d * GT);
+            asm volatile("cp.async.commit_group;\n" ::);
+            asm volatile("cp.async.wait_group 1;\n" ::);
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::);
+        }
+        __syncthreads();
+
+        const int64_t j0 = (int64_t)tj * GT;
+        const bool diag_tile = a.symmetric && (ti == tj);
+        const bool mirror = a.symmetric && !a.lower_only && !diag_tile;
+        const bool full_tile = vec_ok && !diag_tile && (i0 + GT <= a.Na) && (j0 + GT <= a.Nb);   // uniform
+
+        for (int pass = 0; pass < 2; ++pass) {
+            const int lj0 = pass * (GT / 2) + 2 * tx;
+            double r2[4][2], S[NS][4][2];
+#pragma unroll
+            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib) {
+                    r2[ia][ib] = 0.0;
+#pragma unroll
+                    for (int q = 0; q < NS; ++q) S[q][ia][ib] = 0.0;
+                }
+            for (int dd = 0; dd < d; ++dd) {
+                const double2 a01 = *reinterpret_cast<const double2*>(&xa[dd * GT + 4 * ty]);
+                const double2 a23 = *reinterpret_cast<const double2*>(&xa[dd * GT + 4 * ty + 2]);
+                const double2 b01 = *reinterpret_cast<const double2*>(&xbc[dd * GT + lj0]);
+                const double va[4] = {a01.x, a01.y, a23.x, a23.y};
+                const double vb[2] = {b01.x, b01.y};
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) {
+                        const double dx = va[ia] - vb[ib];
+                        r2[ia][ib] = fma(dx, dx, r2[ia][ib]);
+                    }
+            }
+#pragma unroll
+            for (int q = 0; q < NPER; ++q) {
+                for (int dd = 0; dd < d; ++dd) {
+                    double2 ca[4], cb[2];
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia) ca[ia] = fa[(q * d + dd) * GT + 4 * ty + ia];
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) cb[ib] = fbc[(q * d + dd) * GT + lj0 + ib];
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                        for (int ib = 0; ib < 2; ++ib)
+                            S[q][ia][ib] = fma(ca[ia].x, cb[ib].x, fma(ca[ia].y, cb[ib].y, S[q][ia][ib]));
+                }
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) S[q][ia][ib] = fmax(0.0, 0.5 * ((double)d - S[q][ia][ib]));
+            }
+
+            double acc[4][2];
+#pragma unroll
+            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib) acc[ia][ib] = 0.0;
+            for (int t = 0; t < P.nterms; ++t) {
+                const int k0 = P.term_start[t], k1 = P.term_start[t + 1];
+                if (k1 - k0 == 1) {
+                    leaf8<2, NS>(P, P.term_leaf[k0], r2, S, acc);
+                } else {
+                    double prod[4][2];
+                    leaf8<0, NS>(P, P.term_leaf[k0], r2, S, prod);
+                    for (int k = k0 + 1; k < k1; ++k) leaf8<1, NS>(P, P.term_leaf[k], r2, S, prod);
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                        for (int ib = 0; ib < 2; ++ib) acc[ia][ib] += prod[ia][ib];
+                }
+            }
+
+            if (full_tile) {
+                // interior tile: no bounds, diagonal or triangle logic; 16-byte stores
+                double* o = a.out + (i0 + 4 * ty) * a.ldo + j0 + lj0;
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia) {
+                    *reinterpret_cast<double2*>(o + ia * a.ldo) = make_double2(acc[ia][0], acc[ia][1]);
+                    // largest |high word|: >= 0x7ff00000 means an Inf or NaN was produced
+                    expmax = max(expmax, max(__double2hiint(acc[ia][0]) & 0x7fffffff, __double2hiint(acc[ia][1]) & 0x7fffffff));
+                    if (use_tr) {
+                        tr[4 * ty + ia][2 * tx] = acc[ia][0];
+                        tr[4 * ty + ia][2 * tx + 1] = acc[ia][1];
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia) {
+                    const int li = 4 * ty + ia;
+                    const int64_t i = i0 + li, j = j0 + lj0;
+                    if (a.symmetric) {
+                        if (i == j) acc[ia][0] += a.diag_add;
+                        if (i == j + 1) acc[ia][1] += a.diag_add;
+                    }
+                    const bool in0 = (i < a.Na) && (j < a.Nb), in1 = (i < a.Na) && (j + 1 < a.Nb);
+                    if ((in0 && !isfinite(acc[ia][0])) || (in1 && !isfinite(acc[ia][1]))) bad = 1;
+                    const bool tri = a.symmetric && a.lower_only && diag_tile;   // keep only j <= i
+                    if (vec_ok && in1 && !(tri && j + 1 > i)) {
+                        *reinterpret_cast<double2*>(&a.out[i * a.ldo + j]) = make_double2(acc[ia][0], acc[ia][1]);
+                    } else {
+                        if (in0 && !(tri && j > i)) a.out[i * a.ldo + j] = acc[ia][0];
+                        if (in1 && !(tri && j + 1 > i)) a.out[i * a.ldo + j + 1] = acc[ia][1];
+                    }
+                    if (mirror) {
+                        tr[li][2 * tx] = acc[ia][0];
+                        tr[li][2 * tx + 1] = acc[ia][1];
+                    }
+                }
+            }
+            if (use_tr) {   // uniform over the grid: the barriers below are reached by every thread
+                __syncthreads();
+                if (mirror) {
+                    for (int e = tid; e < GT * (GT / 2); e += GTHREADS) {
+                        const int r = e / GT, cc = e - r * GT;
+                        const int64_t j = j0 + pass * (GT / 2) + r, i = i0 + cc;
+                        if (j < a.Nb && i < a.Na) a.out[j * a.ldo + i] = tr[cc][r];
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        __syncthreads();   // every warp is done with this column buffer before the next prefetch overwrites it
+    }
+    if (expmax >= 0x7ff00000) bad = 1;
+    if (a.nonfinite && __syncthreads_or(bad) && tid == 0) atomicAdd(a.nonfinite, 1);
+}
+
+// shared memory of gram_rows_kernel<NPER> for d resident dimensions
+template <int NPER>
+size_t gram_rows_smem(int d, bool use_tr) {
+    return sizeof(double) * 3 * d * GT + sizeof(double2) * 3 * NPER * d * GT + (use_tr ? sizeof(double) * GT * (GT / 2 + 1) : 0);
+}
+
+template <int NPER>
+int launch_gram_rows(Ctx* c, const GramArgs& a, const DevProg& P, int vec_ok, bool* launched) {
+    const bool use_tr = a.symmetric && !a.lower_only;
+    const size_t smem = gram_rows_smem<NPER>(a.d, use_tr);
+    *launched = false;
+    if (smem > 200 * 1024) return 0;   // too many dimensions to keep resident: chunked kernel
+    const int64_t ta = (a.Na + GT - 1) / GT;
+    if (ta > 65535) return 0;
+    static size_t configured = 0;   // per instantiation
+    if (smem > configured) {
+        GP_CUDA(c, cudaFuncSetAttribute(gram_rows_kernel<NPER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    dim3 grid((unsigned)((a.tiles_b + GGROUP - 1) / GGROUP), (unsigned)ta);
+    gram_rows_kernel<NPER><<<grid, GTHREADS, smem, c->stream>>>(a, P, vec_ok, use_tr ? 1 : 0);
+    *launched = true;
+    return 0;
+}
+
+template <int NPER>
+int launch_gram_value(Ctx* c, const GramArgs& a, const DevProg& P, int vec_ok, int64_t grid) {
+    const size_t smem = sizeof(double) * 2 * GDC * GT + sizeof(double2) * 2 * NPER * GDC * GT + sizeof(double) * GT * (GT / 2 + 1);
+    static bool configured = false;   // per instantiation
+    if (!configured) {
+        GP_CUDA(c, cudaFuncSetAttribute(gram_value_kernel<NPER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    gram_value_kernel<NPER><<<(unsigned)grid, GTHREADS, smem, c->stream>>>(a, P, vec_ok);
+    return 0;
+}
+
 // F[row][leaf][dim] = (cos, sin)(2 b_leaf x[row][dim]) for the PERIODIC leaves of the kernel tree
 __global__ void periodic_features_kernel(const double* X, int64_t n, int d, DevProg P, double* F) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -388,6 +938,47 @@ int lower_program(const KProg& in, DevProg* out, std::string* err) {
         return -2;
     }
     D.nper = nper;
+    // expand the tree into a sum of products of leaves (distributing products over sums)
+    {
+        typedef std::vector<std::vector<int>> Poly;   // list of terms, each a list of leaf op indices
+        std::vector<Poly> st;
+        bool ok = true;
+        for (int i = 0; i < in.nops && ok; ++i) {
+            const int op = in.op[i];
+            if (op == GPRB200_K_SUM || op == GPRB200_K_PRODUCT) {
+                Poly b = st.back(); st.pop_back();
+                Poly a = st.back(); st.pop_back();
+                Poly r;
+                if (op == GPRB200_K_SUM) {
+                    r = a;
+                    r.insert(r.end(), b.begin(), b.end());
+                } else {
+                    for (const auto& ta : a)
+                        for (const auto& tb : b) {
+                            std::vector<int> t = ta;
+                            t.insert(t.end(), tb.begin(), tb.end());
+                            r.push_back(t);
+                        }
+                }
+                size_t leaves = 0;
+                for (const auto& t : r) leaves += t.size();
+                if (r.size() > (size_t)MAX_TERMS || leaves > (size_t)MAX_TERM_LEAVES) ok = false;
+                st.push_back(r);
+            } else {
+                st.push_back(Poly{{i}});
+            }
+        }
+        D.nterms = 0;
+        if (ok && st.size() == 1) {
+            int k = 0, t = 0;
+            for (const auto& term : st[0]) {
+                D.term_start[t++] = (int8_t)k;
+                for (int leaf : term) D.term_leaf[k++] = (int8_t)leaf;
+            }
+            D.term_start[t] = (int8_t)k;
+            D.nterms = t;
+        }
+    }
     return 0;
 }
 
@@ -425,7 +1016,29 @@ int gram_build(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t N
         }
         GP_CUDA(c, cudaGetLastError());
     }
-    gram_kernel<false><<<(unsigned)grid, GTHREADS, 0, c->stream>>>(a, P);
+    const int vec_ok = ((ldo & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
+    bool launched = false;
+    if (P.nterms > 0 && c->opt_gram_terms >= 2) {
+        switch (P.nper) {
+            case 0: GP_TRY(launch_gram_rows<0>(c, a, P, vec_ok, &launched)); break;
+            case 1: GP_TRY(launch_gram_rows<1>(c, a, P, vec_ok, &launched)); break;
+            case 2: GP_TRY(launch_gram_rows<2>(c, a, P, vec_ok, &launched)); break;
+            case 3: GP_TRY(launch_gram_rows<3>(c, a, P, vec_ok, &launched)); break;
+            default: GP_TRY(launch_gram_rows<4>(c, a, P, vec_ok, &launched)); break;
+        }
+    }
+    if (launched) {
+    } else if (P.nterms > 0 && c->opt_gram_terms) {
+        switch (P.nper) {
+            case 0: GP_TRY(launch_gram_value<0>(c, a, P, vec_ok, grid)); break;
+            case 1: GP_TRY(launch_gram_value<1>(c, a, P, vec_ok, grid)); break;
+            case 2: GP_TRY(launch_gram_value<2>(c, a, P, vec_ok, grid)); break;
+            case 3: GP_TRY(launch_gram_value<3>(c, a, P, vec_ok, grid)); break;
+            default: GP_TRY(launch_gram_value<4>(c, a, P, vec_ok, grid)); break;
+        }
+    } else {
+        gram_kernel<false><<<(unsigned)grid, GTHREADS, 0, c->stream>>>(a, P);   // interpreter: any tree
+    }
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     if (feat) GP_CUDA(c, cudaFreeAsync(feat, c->stream));

@@ -17,6 +17,8 @@
 namespace gprb200 {
 
 constexpr int MAXPER = 4;  // PERIODIC leaves per kernel tree handled in one pass
+constexpr int MAX_TERMS = 12;        // expanded sum-of-products form of the kernel value
+constexpr int MAX_TERM_LEAVES = 24;  // leaf evaluations over all terms
 
 // Device form of the program: per-op derived constants are precomputed on the host in fp64.
 struct DevProg {
@@ -31,6 +33,11 @@ struct DevProg {
     int8_t perslot[GPRB200_MAX_OPS];  // PERIODIC leaf -> slot in the per-pair S/F accumulators
     double cst[GPRB200_MAX_OPS][6];
     double perb[MAXPER];  // b of each periodic leaf
+    // Term form of the value: k = sum_t prod_{l in term t} leaf_l, the Sum/Product tree expanded on the host
+    // (lower_program). nterms == 0: the expansion was too large, the value kernels fall back to the interpreter.
+    int nterms;
+    int8_t term_start[MAX_TERMS + 1];   // term t = term_leaf[term_start[t] .. term_start[t+1])
+    int8_t term_leaf[MAX_TERM_LEAVES];  // op index of the leaf (its constants are cst[that index])
 };
 
 // geometry of one (x, y) pair

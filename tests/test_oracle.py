@@ -18,7 +18,7 @@ from oracle import ref
 from tests.synth import KERNELS, make_problem, rel_err
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")) if "clamp" not in f and "pca_" not in f and "infer_" not in f and "sparse_" not in f)
+CASES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")) if "clamp" not in f and "pca_" not in f and "infer_" not in f and "sparse" not in f)
 
 
 def load(name):
