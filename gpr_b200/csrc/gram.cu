@@ -552,8 +552,10 @@ __device__ __forceinline__ void leaf8(const DevProg& P, int node, const double (
             for (int ia = 0; ia < 4; ++ia)
 #pragma unroll
                 for (int ib = 0; ib < 2; ++ib) {
+                    // RQ: f^-alpha = exp(-alpha ln f), f >= 1 (relative error <= (1 + alpha ln f) ulp)
                     const double v = (op == GPRB200_K_WHITE) ? ((r2[ia][ib] == 0.0) ? c0 : 0.0)
-                                                             : c0 * pow(fma(c1, r2[ia][ib], 1.0), c2);   // RQ
+                                     : (c2 <= 0.0)           ? c0 * exp_nonpos(c2 * log(fma(c1, r2[ia][ib], 1.0)))
+                                                             : c0 * pow(fma(c1, r2[ia][ib], 1.0), c2);
                     if (MODE == 0) dst[ia][ib] = v;
                     else if (MODE == 1) dst[ia][ib] *= v;
                     else dst[ia][ib] += v;
@@ -751,6 +753,248 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_rows_kernel(GramArgs a, DevP
     if (a.nonfinite && __syncthreads_or(bad) && tid == 0) atomicAdd(a.nonfinite, 1);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused derivative contraction out[p] = sum_ij W_ij dK_p(xa_i, xb_j) (K2: the trace 1/2 tr((alpha alpha^T - C) dK_p)
+// of include/Likelihood.h:280-282 and the two sums of the sparse likelihood) in the same row-group / term form as
+// gram_rows_kernel. dK is never stored. Every leaf derivative of the family is leaf value x constant x a factor of
+// the pair geometry (r^2; S, F for PERIODIC; r^2/f, ln f for RQ), so for a term t = prod_l leaf_l
+//     d t / d theta_p = t x dcst_p x factor_p          (p a parameter of a leaf of t)
+// and one weighted product g = W t per pair serves every parameter of the term. Per-thread sums live in shared memory
+// ([P][256], the thread's own column: no synchronisation), reduced once per CTA in a fixed order (deterministic).
+template <int NPER>
+__global__ void __launch_bounds__(GTHREADS, 2) gram_dcontract_kernel(GramArgs a, DevProg P, int vec_ok) {
+    constexpr int NS = NPER > 0 ? NPER : 1;
+    extern __shared__ __align__(16) unsigned char gv_smem[];
+    const int d = a.d;
+    double* xa = reinterpret_cast<double*>(gv_smem);
+    double* xb = xa + d * GT;
+    double2* fa = reinterpret_cast<double2*>(xb + 2 * d * GT);
+    double2* fb = fa + NPER * d * GT;
+    double* accs = reinterpret_cast<double*>(fb + 2 * NPER * d * GT);   // [nparams][GTHREADS]
+
+    const int ti = blockIdx.y;
+    const int tj_begin = blockIdx.x * GGROUP;
+    int tj_end = min(tj_begin + GGROUP, a.tiles_b);
+    if (a.symmetric) tj_end = min(tj_end, ti + 1);
+    if (tj_begin >= tj_end) return;   // its partial row stays at the memset zero
+    const int64_t i0 = (int64_t)ti * GT;
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    for (int p = 0; p < P.nparams; ++p) accs[p * GTHREADS + tid] = 0.0;
+
+    auto stage_side = [&](const double* X, const double* F, int64_t row0, int64_t nrows, double* xs, double2* fs) {
+        for (int e = tid; e < GT * d; e += GTHREADS) {
+            const int r = e & (GT - 1), dd = e / GT;
+            if (row0 + r < nrows) {
+                cp_async8(&xs[dd * GT + r], X + (row0 + r) * d + dd);
+#pragma unroll
+                for (int q = 0; q < NPER; ++q)
+                    cp_async16(&fs[(q * d + dd) * GT + r], F + (((row0 + r) * NPER + q) * d + dd) * 2);
+            } else {
+                xs[dd * GT + r] = 0.0;
+#pragma unroll
+                for (int q = 0; q < NPER; ++q) fs[(q * d + dd) * GT + r] = make_double2(1.0, 0.0);
+            }
+        }
+    };
+    stage_side(a.Xa, a.Fa, i0, a.Na, xa, fa);
+    stage_side(a.Xb, a.Fb, (int64_t)tj_begin * GT, a.Nb, xb, fb);
+    asm volatile("cp.async.commit_group;\n" ::);
+
+    for (int tj = tj_begin; tj < tj_end; ++tj) {
+        const int buf = (tj - tj_begin) & 1;
+        const double* xbc = xb + buf * d * GT;
+        const double2* fbc = fb + buf * NPER * d * GT;
+        if (tj + 1 < tj_end) {
+            stage_side(a.Xb, a.Fb, (int64_t)(tj + 1) * GT, a.Nb, xb + (buf ^ 1) * d * GT, fb + (buf ^ 1) * NPER * d * GT);
+            asm volatile("cp.async.commit_group;\n" ::);
+            asm volatile("cp.async.wait_group 1;\n" ::);
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::);
+        }
+        __syncthreads();
+
+        const int64_t j0 = (int64_t)tj * GT;
+        const bool diag_tile = a.symmetric && (ti == tj);
+        const double wscale = (a.symmetric && !diag_tile) ? 2.0 : 1.0;   // symmetric W and dK: off-diagonal tiles count twice
+        const bool full_tile = vec_ok && (i0 + GT <= a.Na) && (j0 + GT <= a.Nb);
+
+        for (int pass = 0; pass < 2; ++pass) {
+            const int lj0 = pass * (GT / 2) + 2 * tx;
+            double w[4][2];
+            if (full_tile) {
+                const double* wp = a.S + (i0 + 4 * ty) * a.lds + j0 + lj0;
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia) {
+                    const double2 t = __ldg(reinterpret_cast<const double2*>(wp + ia * a.lds));
+                    w[ia][0] = t.x * wscale;
+                    w[ia][1] = t.y * wscale;
+                }
+            } else {
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) {
+                        const int64_t i = i0 + 4 * ty + ia, j = j0 + lj0 + ib;
+                        w[ia][ib] = (i < a.Na && j < a.Nb) ? a.S[i * a.lds + j] * wscale : 0.0;
+                    }
+            }
+            double r2[4][2], S[NS][4][2], F[NS][4][2];
+#pragma unroll
+            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib) {
+                    r2[ia][ib] = 0.0;
+#pragma unroll
+                    for (int q = 0; q < NS; ++q) S[q][ia][ib] = F[q][ia][ib] = 0.0;
+                }
+            for (int dd = 0; dd < d; ++dd) {
+                const double2 a01 = *reinterpret_cast<const double2*>(&xa[dd * GT + 4 * ty]);
+                const double2 a23 = *reinterpret_cast<const double2*>(&xa[dd * GT + 4 * ty + 2]);
+                const double2 b01 = *reinterpret_cast<const double2*>(&xbc[dd * GT + lj0]);
+                const double va[4] = {a01.x, a01.y, a23.x, a23.y};
+                const double vb[2] = {b01.x, b01.y};
+                double dx[4][2];
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) {
+                        dx[ia][ib] = va[ia] - vb[ib];
+                        r2[ia][ib] = fma(dx[ia][ib], dx[ia][ib], r2[ia][ib]);
+                    }
+#pragma unroll
+                for (int q = 0; q < NPER; ++q) {
+                    // cos / sin of 2 b dx from the per-point features: S accumulates cos (turned into sum sin^2 below),
+                    // F = sum_d dx sin(2 b dx) = sum_d 2 dx cos(b dx) sin(b dx)   (include/Kernel.h:930-941)
+                    double2 ca[4], cb[2];
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia) ca[ia] = fa[(q * d + dd) * GT + 4 * ty + ia];
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) cb[ib] = fbc[(q * d + dd) * GT + lj0 + ib];
+#pragma unroll
+                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                        for (int ib = 0; ib < 2; ++ib) {
+                            S[q][ia][ib] = fma(ca[ia].x, cb[ib].x, fma(ca[ia].y, cb[ib].y, S[q][ia][ib]));
+                            const double sn = fma(ca[ia].y, cb[ib].x, -(ca[ia].x * cb[ib].y));
+                            F[q][ia][ib] = fma(dx[ia][ib], sn, F[q][ia][ib]);
+                        }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < NPER; ++q)
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) S[q][ia][ib] = fmax(0.0, 0.5 * ((double)d - S[q][ia][ib]));
+
+            for (int t = 0; t < P.nterms; ++t) {
+                const int k0 = P.term_start[t], k1 = P.term_start[t + 1];
+                double g[4][2];
+                leaf8<0, NS>(P, P.term_leaf[k0], r2, S, g);
+                for (int k = k0 + 1; k < k1; ++k) leaf8<1, NS>(P, P.term_leaf[k], r2, S, g);
+                double sg = 0.0;
+#pragma unroll
+                for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib) {
+                        g[ia][ib] *= w[ia][ib];
+                        sg += g[ia][ib];
+                    }
+                for (int k = k0; k < k1; ++k) {
+                    const int node = P.term_leaf[k];
+                    const int op = P.op[node];
+                    double* o = accs + (int)P.poff[node] * GTHREADS + tid;
+                    const double dc0 = P.dcst[node][0], dc1 = P.dcst[node][1], dc2 = P.dcst[node][2];
+                    switch (op) {
+                        case GPRB200_K_GAUSSIAN:
+                        case GPRB200_K_GAUSSIAN_EXP: {
+                            double s0 = 0.0;
+#pragma unroll
+                            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                                for (int ib = 0; ib < 2; ++ib) s0 = fma(g[ia][ib], r2[ia][ib], s0);
+                            o[0] = fma(dc0, s0, o[0]);
+                            o[GTHREADS] = fma(dc1, sg, o[GTHREADS]);
+                        } break;
+                        case GPRB200_K_WHITE:
+                            o[0] = fma(dc0, sg, o[0]);
+                            break;
+                        case GPRB200_K_RQ: {
+                            const double c1 = P.cst[node][1];
+                            double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+                            for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                                for (int ib = 0; ib < 2; ++ib) {
+                                    const double f = fma(c1, r2[ia][ib], 1.0);
+                                    const double q1 = r2[ia][ib] / f;
+                                    s1 = fma(g[ia][ib], q1, s1);
+                                    s2 = fma(g[ia][ib], fma(c1, q1, -log(f)), s2);
+                                }
+                            o[0] = fma(dc0, sg, o[0]);
+                            o[GTHREADS] = fma(dc1, s1, o[GTHREADS]);
+                            o[2 * GTHREADS] = fma(dc2, s2, o[2 * GTHREADS]);
+                        } break;
+                        default: {  // PERIODIC [scale, b, sigma]
+                            const int slot = P.perslot[node];
+                            double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+                            for (int q = 0; q < NS; ++q)
+                                if (slot == q) {
+#pragma unroll
+                                    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+                                        for (int ib = 0; ib < 2; ++ib) {
+                                            s1 = fma(g[ia][ib], F[q][ia][ib], s1);
+                                            s2 = fma(g[ia][ib], S[q][ia][ib], s2);
+                                        }
+                                }
+                            o[0] = fma(dc0, sg, o[0]);
+                            o[GTHREADS] = fma(dc1, s1, o[GTHREADS]);
+                            o[2 * GTHREADS] = fma(dc2, s2, o[2 * GTHREADS]);
+                        } break;
+                    }
+                }
+            }
+        }
+        __syncthreads();   // every warp is done with this column buffer before the next prefetch overwrites it
+    }
+
+    // deterministic CTA reduction: warp shuffle, then the 8 warp sums in order
+    __shared__ double red[GTHREADS / 32];
+    double* out = a.partial + ((int64_t)blockIdx.y * gridDim.x + blockIdx.x) * P.nparams;
+    for (int p = 0; p < P.nparams; ++p) {
+        double v = accs[p * GTHREADS + tid];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        __syncthreads();
+        if ((tid & 31) == 0) red[tid >> 5] = v;
+        __syncthreads();
+        if (tid == 0) {
+            double s = 0.0;
+            for (int wv = 0; wv < GTHREADS / 32; ++wv) s += red[wv];
+            out[p] = s;
+        }
+    }
+}
+
+template <int NPER>
+int launch_gram_dcontract(Ctx* c, const GramArgs& a, const DevProg& P, int vec_ok, dim3 grid, bool* launched) {
+    const size_t smem = sizeof(double) * 3 * a.d * GT + sizeof(double2) * 3 * NPER * a.d * GT +
+                        sizeof(double) * (size_t)P.nparams * GTHREADS;
+    *launched = false;
+    if (smem > 200 * 1024) return 0;
+    static size_t configured = 0;
+    if (smem > configured) {
+        GP_CUDA(c, cudaFuncSetAttribute(gram_dcontract_kernel<NPER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    gram_dcontract_kernel<NPER><<<grid, GTHREADS, smem, c->stream>>>(a, P, vec_ok);
+    *launched = true;
+    return 0;
+}
+
 // shared memory of gram_rows_kernel<NPER> for d resident dimensions
 template <int NPER>
 size_t gram_rows_smem(int d, bool use_tr) {
@@ -864,6 +1108,8 @@ int lower_program(const KProg& in, DevProg* out, std::string* err) {
                 c[1] = -0.5 / (sg * sg);
                 c[2] = (s * s) / (sg * sg * sg);
                 c[3] = 2.0 * s;
+                D.dcst[i][0] = 1.0 / (sg * sg * sg);            // x r^2
+                D.dcst[i][1] = (s != 0.0) ? 2.0 / s : 0.0;      // x 1
                 poff += 2;
             } break;
             case GPRB200_K_GAUSSIAN_EXP: {
@@ -875,12 +1121,16 @@ int lower_program(const KProg& in, DevProg* out, std::string* err) {
                 c[2] = exp(-2.0 * sg);
                 c[3] = (4.0 * sg - 4.0 * s) * exp(2.0 * sg);
                 c[4] = 4.0 * exp(2.0 * sg) * s;
+                // include/Kernel.h:591-596: d/dsigma = r^2 exp(-2 sigma) k, d/dscale = 2 k
+                D.dcst[i][0] = exp(-2.0 * sg);
+                D.dcst[i][1] = 2.0;
                 poff += 2;
             } break;
             case GPRB200_K_WHITE: {
                 if (!need(1)) return -2;
                 c[0] = th[0] * th[0];
                 c[1] = 2.0 * th[0];
+                D.dcst[i][0] = (th[0] != 0.0) ? 2.0 / th[0] : 0.0;
                 poff += 1;
             } break;
             case GPRB200_K_RQ: {
@@ -891,6 +1141,9 @@ int lower_program(const KProg& in, DevProg* out, std::string* err) {
                 c[2] = -al;
                 c[3] = 2.0 * s;
                 c[4] = (s * s) / (sg * sg * sg);
+                D.dcst[i][0] = (s != 0.0) ? 2.0 / s : 0.0;      // x 1
+                D.dcst[i][1] = 1.0 / (sg * sg * sg);            // x r^2 / f
+                D.dcst[i][2] = 1.0;                             // x (r^2 / (2 sg^2 a f) - ln f)
                 poff += 3;
             } break;
             case GPRB200_K_PERIODIC: {
@@ -904,6 +1157,9 @@ int lower_program(const KProg& in, DevProg* out, std::string* err) {
                 c[1] = -0.5 / (sg * sg);
                 c[2] = 2.0 * s;
                 c[3] = (s * s) / (sg * sg * sg);
+                D.dcst[i][0] = (s != 0.0) ? 2.0 / s : 0.0;      // x 1
+                D.dcst[i][1] = -0.5 / (sg * sg);                // x F = sum_d dx sin(2 b dx)
+                D.dcst[i][2] = 1.0 / (sg * sg * sg);            // x S = sum_d sin^2(b dx)
                 D.perb[nper] = b;
                 D.perslot[i] = (int8_t)nper;
                 ++nper;
@@ -1089,12 +1345,61 @@ int dgram_contract_xy(Ctx* c, const double* Xa, int64_t Na, const double* Xb, in
     if (int r = lower_program(c->prog, &P, &c->err)) return r;
     const bool symmetric = (Xa == Xb && Na == Nb);
     const int64_t ta = (Na + GT - 1) / GT, tb = (Nb + GT - 1) / GT;
+    GramArgs a{};
+    a.Xa = Xa; a.Xb = Xb; a.Na = Na; a.Nb = Nb; a.d = c->d;
+    a.symmetric = symmetric ? 1 : 0; a.S = W; a.lds = ldw; a.tiles_b = (int)tb; a.p_select = -1;
+
+    if (P.nterms > 0 && c->opt_gram_terms >= 2 && ta <= 65535) {
+        // row-group term-form kernel (gram_dcontract_kernel)
+        dim3 grid((unsigned)((tb + GGROUP - 1) / GGROUP), (unsigned)ta);
+        const int64_t nblocks = (int64_t)grid.x * grid.y;
+        double* partial = nullptr;
+        double* feat = nullptr;
+        GP_CUDA(c, cudaMallocAsync(&partial, sizeof(double) * (nblocks + 1) * P.nparams, c->stream));
+        GP_CUDA(c, cudaMemsetAsync(partial, 0, sizeof(double) * nblocks * P.nparams, c->stream));
+        if (P.nper > 0) {
+            const int64_t per_row = (int64_t)P.nper * c->d * 2;
+            GP_CUDA(c, cudaMallocAsync((void**)&feat, sizeof(double) * per_row * (Na + (symmetric ? 0 : Nb)), c->stream));
+            periodic_features_kernel<<<(unsigned)((Na * P.nper * c->d + 255) / 256), 256, 0, c->stream>>>(Xa, Na, c->d, P, feat);
+            ++c->launches;
+            a.Fa = a.Fb = feat;
+            if (!symmetric) {
+                a.Fb = feat + per_row * Na;
+                periodic_features_kernel<<<(unsigned)((Nb * P.nper * c->d + 255) / 256), 256, 0, c->stream>>>(
+                    Xb, Nb, c->d, P, feat + per_row * Na);
+                ++c->launches;
+            }
+        }
+        a.partial = partial;
+        const int vec_ok = ((ldw & 1) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0) ? 1 : 0;
+        bool launched = false;
+        switch (P.nper) {
+            case 0: GP_TRY(launch_gram_dcontract<0>(c, a, P, vec_ok, grid, &launched)); break;
+            case 1: GP_TRY(launch_gram_dcontract<1>(c, a, P, vec_ok, grid, &launched)); break;
+            case 2: GP_TRY(launch_gram_dcontract<2>(c, a, P, vec_ok, grid, &launched)); break;
+            case 3: GP_TRY(launch_gram_dcontract<3>(c, a, P, vec_ok, grid, &launched)); break;
+            default: GP_TRY(launch_gram_dcontract<4>(c, a, P, vec_ok, grid, &launched)); break;
+        }
+        if (launched) {
+            ++c->launches;
+            GP_CUDA(c, cudaGetLastError());
+            double* dres = partial + nblocks * P.nparams;
+            reduce_partials_kernel<<<P.nparams, 32, 0, c->stream>>>(partial, (int)nblocks, P.nparams, dres);
+            ++c->launches;
+            GP_CUDA(c, cudaGetLastError());
+            GP_CUDA(c, cudaMemcpyAsync(out_host, dres, sizeof(double) * P.nparams, cudaMemcpyDeviceToHost, c->stream));
+            GP_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+        if (feat) GP_CUDA(c, cudaFreeAsync(feat, c->stream));
+        GP_CUDA(c, cudaFreeAsync(partial, c->stream));
+        if (launched) return 0;
+    }
+
+    // per-entry interpreter (any tree, any d)
     const int64_t grid = symmetric ? sym_tiles(ta) : ta * tb;
     double* partial = nullptr;
     GP_CUDA(c, cudaMallocAsync(&partial, sizeof(double) * (grid + 1) * P.nparams, c->stream));
-    GramArgs a{};
-    a.Xa = Xa; a.Xb = Xb; a.Na = Na; a.Nb = Nb; a.d = c->d;
-    a.symmetric = symmetric ? 1 : 0; a.S = W; a.lds = ldw; a.partial = partial; a.tiles_b = (int)tb; a.p_select = -1;
+    a.partial = partial;
     gram_kernel<true><<<(unsigned)grid, GTHREADS, 0, c->stream>>>(a, P);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());

@@ -38,6 +38,9 @@ struct DevProg {
     int nterms;
     int8_t term_start[MAX_TERMS + 1];   // term t = term_leaf[term_start[t] .. term_start[t+1])
     int8_t term_leaf[MAX_TERM_LEAVES];  // op index of the leaf (its constants are cst[that index])
+    // d leaf / d theta_p = leaf value x dcst[p] x factor_p(r^2, S, F): every leaf derivative of the family is
+    // proportional to the leaf value (gram_dcontract_kernel); 0 where the scale parameter is 0
+    double dcst[GPRB200_MAX_OPS][3];
 };
 
 // geometry of one (x, y) pair
