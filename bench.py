@@ -332,6 +332,20 @@ def run_gpu(args):
             },
             "residual": resid,
         }
+        gram_ms = phases["gram"] / args.steps
+        hbm_peak = (peaks or {}).get("hbm_gbs", 6650.0)
+        # C3 kernel per pair: 2d (difference, square) + 2d (PERIODIC trig-feature dot product) + 2 x ~20 (two exponentials) + ~5
+        gram_fp64_per_pair = 2 * d + 2 * d + 2 * 20 + 5
+        gram_floor_ms = (N * (N + 1) / 2.0) * gram_fp64_per_pair / (FP64_PEAK_TFLOPS / 2.0 * 1e12) * 1e3
+        line["gram"] = {
+            "kernel": "gram_rows_kernel<1> (term form, lower triangle only, 4 N^2 bytes written)",
+            "ms": gram_ms, "bytes_written": 4.0 * N * N, "achieved_gbs": 4.0 * N * N / gram_ms * 1e-6,
+            "frac_of_hbm_peak": 4.0 * N * N / gram_ms * 1e-6 / hbm_peak, "bound": "fp64 alu",
+            "fp64_instr_per_pair": gram_fp64_per_pair, "fp64_floor_ms": gram_floor_ms,
+            "frac_of_fp64_floor": gram_floor_ms / gram_ms if gram_ms else None,
+            "note": "FP64-ALU-bound, not HBM-bound, for this kernel family at d = 8: the DFMA pipe (half of the 37.1 TFLOP/s "
+                    "FMA rate counted as instructions) needs fp64_floor_ms; HBM would need %.2f ms" % (4.0 * N * N / hbm_peak * 1e-6),
+        }
         if predict:
             line["predict"] = predict
         if large:

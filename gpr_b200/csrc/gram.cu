@@ -502,7 +502,7 @@ __device__ __forceinline__ void exp_leaf8(const double (&src)[4][2], double c0, 
     for (int ia = 0; ia < 4; ++ia)
 #pragma unroll
         for (int ib = 0; ib < 2; ++ib) {
-            const double x = c1 * src[ia][ib];
+            const double x = __dmul_rn(c1, src[ia][ib]);
             const double t = fma(x, 1.4426950408889634074, MAGIC);
             n[ia][ib] = __double2loint(t);
             const double nd = t - MAGIC;
@@ -524,9 +524,11 @@ __device__ __forceinline__ void exp_leaf8(const double (&src)[4][2], double c0, 
         for (int ib = 0; ib < 2; ++ib) {
             double v = __hiloint2double(__double2hiint(p[ia][ib]) + (n[ia][ib] << 20), __double2loint(p[ia][ib]));
             v = (n[ia][ib] < -1021) ? 0.0 : v;     // below 2^-1022: no denormal path
-            if (MODE == 0) dst[ia][ib] = c0 * v;
-            else if (MODE == 1) dst[ia][ib] *= c0 * v;
-            else dst[ia][ib] = fma(c0, v, dst[ia][ib]);
+            // explicit roundings: K(i,j) and K(j,i) of a diagonal tile sit in different register slots of different
+            // threads and must come out bit-identical, so the compiler may not choose the mul/add contractions
+            if (MODE == 0) dst[ia][ib] = __dmul_rn(c0, v);
+            else if (MODE == 1) dst[ia][ib] = __dmul_rn(dst[ia][ib], __dmul_rn(c0, v));
+            else dst[ia][ib] = __fma_rn(c0, v, dst[ia][ib]);
         }
 }
 
@@ -554,11 +556,11 @@ __device__ __forceinline__ void leaf8(const DevProg& P, int node, const double (
                 for (int ib = 0; ib < 2; ++ib) {
                     // RQ: f^-alpha = exp(-alpha ln f), f >= 1 (relative error <= (1 + alpha ln f) ulp)
                     const double v = (op == GPRB200_K_WHITE) ? ((r2[ia][ib] == 0.0) ? c0 : 0.0)
-                                     : (c2 <= 0.0)           ? c0 * exp_nonpos(c2 * log(fma(c1, r2[ia][ib], 1.0)))
-                                                             : c0 * pow(fma(c1, r2[ia][ib], 1.0), c2);
+                                     : (c2 <= 0.0) ? __dmul_rn(c0, exp_nonpos(__dmul_rn(c2, log(__fma_rn(c1, r2[ia][ib], 1.0)))))
+                                                   : __dmul_rn(c0, pow(__fma_rn(c1, r2[ia][ib], 1.0), c2));
                     if (MODE == 0) dst[ia][ib] = v;
-                    else if (MODE == 1) dst[ia][ib] *= v;
-                    else dst[ia][ib] += v;
+                    else if (MODE == 1) dst[ia][ib] = __dmul_rn(dst[ia][ib], v);
+                    else dst[ia][ib] = __dadd_rn(dst[ia][ib], v);
                 }
         } break;
     }
@@ -675,7 +677,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_rows_kernel(GramArgs a, DevP
 #pragma unroll
                 for (int ia = 0; ia < 4; ++ia)
 #pragma unroll
-                    for (int ib = 0; ib < 2; ++ib) S[q][ia][ib] = fmax(0.0, 0.5 * ((double)d - S[q][ia][ib]));
+                    for (int ib = 0; ib < 2; ++ib) S[q][ia][ib] = fmax(0.0, __dmul_rn(0.5, __dsub_rn((double)d, S[q][ia][ib])));
             }
 
             double acc[4][2];
@@ -694,7 +696,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_rows_kernel(GramArgs a, DevP
 #pragma unroll
                     for (int ia = 0; ia < 4; ++ia)
 #pragma unroll
-                        for (int ib = 0; ib < 2; ++ib) acc[ia][ib] += prod[ia][ib];
+                        for (int ib = 0; ib < 2; ++ib) acc[ia][ib] = __dadd_rn(acc[ia][ib], prod[ia][ib]);
                 }
             }
 
