@@ -23,4 +23,7 @@ for ks in ("GaussianKernel(2,1,)", "SumKernel(SumKernel(GaussianKernel(2,1,),Per
         h._ck(h.lib.gprb200_gram_block_dev(h.h, 0, N, 0, N, out.data_ptr(), N))
     torch.cuda.synchronize()
     print(ks, float(out[5, 7]))
+    # fused derivative contraction (gram_dcontract_kernel) inside one log-likelihood + gradient evaluation
+    v, g, _ = h.loglik(1, True, True, False)
+    print("loglik", v, g)
     h.close()
