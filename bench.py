@@ -283,6 +283,9 @@ def run_gpu(args):
     if rank == 0 and not args.skip_pca:
         pca = run_pca(torch, gpr_b200, local_rank)
 
+    host_io = None
+    if rank == 0 and not args.skip_hostio:
+        host_io = run_host_io(torch, gpr_b200, local_rank)
     sparse = None
     if rank == 0 and not args.skip_sparse:
         sparse = run_sparse(torch, gpr_b200, local_rank)
@@ -356,6 +359,8 @@ def run_gpu(args):
             line["pca_frame"] = pca
         if sparse:
             line["sparse"] = sparse
+        if host_io:
+            line["host_io"] = host_io
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
         if peaks:
@@ -604,6 +609,50 @@ def run_pca(torch, gpr_b200, local_rank, D=3 * 64 ** 3, n=256, nF=32, N=256, d=3
             "round_trip_rel_err": rt, "discarded_energy": tail}
 
 
+def run_host_io(torch, gpr_b200, local_rank, N=4096, d=30, M=196608):
+    """G1 / G5 / G15 at the motion-model shape (a quarter of C2's 786432 columns: Y = 6.4 GB): label vectors stored one
+    allocation per sample (the reference's std::vector<VectorType>) -> device, and the regression vectors back.
+    Streamed (pinned ring, csrc/hostio.cu) against what the same host program does without it: gather the N x M
+    matrix (ComputeLabelMatrixInternal, lib/GaussianProcess.cpp:621-639), then one pageable cudaMemcpy each way."""
+    rng = np.random.default_rng(SEED + 7)
+    X = rng.standard_normal((N, d))
+    rows = [rng.standard_normal(M) for _ in range(N)]
+    h = gpr_b200.Handle(local_rank)
+    ops, params = gpr_b200.KernelFactory.GetKernel(C2_KERNEL).lower()
+    h.set_kernel(ops, params)
+    gb = 8.0 * N * M * 1e-9
+    out = {"shape": [N, M], "gigabytes": gb}
+    xr = [x for x in X]
+    h.set_train_rows(xr, rows, C2_SIGMA)      # warm-up: pinned ring and device buffers allocated
+    t0 = time.perf_counter()
+    h.set_train_rows(xr, rows, C2_SIGMA)
+    out["rows_to_device_s"] = time.perf_counter() - t0
+    h.learn(0)
+    A = np.empty((N, M))
+    h._ck(h.lib.gprb200_get_alpha(h.h, A.ctypes.data))      # warm-up (page faults of the destination)
+    t0 = time.perf_counter()
+    h._ck(h.lib.gprb200_get_alpha(h.h, A.ctypes.data))
+    out["alpha_to_host_s"] = time.perf_counter() - t0
+    h.set_option("stream_io", 0)
+    t0 = time.perf_counter()
+    Y = np.empty((N, M))
+    for i in range(N):
+        Y[i] = rows[i]
+    t1 = time.perf_counter()
+    h.set_train(X, Y, C2_SIGMA)
+    out["gather_s"], out["gather_plus_pageable_to_device_s"] = t1 - t0, time.perf_counter() - t0
+    h.learn(0)
+    t0 = time.perf_counter()
+    h._ck(h.lib.gprb200_get_alpha(h.h, A.ctypes.data))
+    out["alpha_to_host_pageable_s"] = time.perf_counter() - t0
+    h.close()
+    out["rows_to_device_gbs"] = gb / out["rows_to_device_s"]
+    out["alpha_to_host_gbs"] = gb / out["alpha_to_host_s"]
+    out["speedup_to_device"] = out["gather_plus_pageable_to_device_s"] / out["rows_to_device_s"]
+    out["speedup_to_host"] = out["alpha_to_host_pageable_s"] / out["alpha_to_host_s"]
+    return out
+
+
 def run_sparse(torch, gpr_b200, local_rank, n=262144, m=4096, d=8):
     """SURVEY 8(f) row 4: SparseGaussianProcess::PreComputeRegression (include/SparseGaussianProcess.h:274-312) at a
     size whose dense kernel matrix (n^2 * 8 B = 550 GB) does not exist: cross-Gram Knm (n x m), S = K + sigma^-2 Kmn Knm
@@ -757,6 +806,7 @@ def main():
     ap.add_argument("--skip-loglik", action="store_true")
     ap.add_argument("--skip-pca", action="store_true")
     ap.add_argument("--skip-sparse", action="store_true")
+    ap.add_argument("--skip-hostio", action="store_true")
     ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")

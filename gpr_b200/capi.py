@@ -57,6 +57,7 @@ _PROTOS = {
     "gprb200_dgram": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_loglik": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gprb200_quadform": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gprb200_set_train_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_double]),
     "gprb200_sparse_set_inducing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double]),
     "gprb200_sparse_set_jitter": (C.c_int, [C.c_void_p, C.c_double]),
     "gprb200_sparse_learn": (C.c_int, [C.c_void_p]),
@@ -171,6 +172,16 @@ class Handle:
         self.N, self.d = X.shape
         self.M = Y.shape[1] if Y is not None else 0
         self._ck(self.lib.gprb200_set_train(self.h, _ptr(X), self.N, self.d, _ptr(Y), self.M, float(sigma)))
+
+    def set_train_rows(self, Xrows, Yrows, sigma):
+        """one numpy vector per sample / label (the reference's vector-of-vectors storage); labels are streamed"""
+        Xrows = [_f64(x).ravel() for x in Xrows]
+        Yrows = [_f64(y).ravel() for y in Yrows] if Yrows is not None else None
+        self.N, self.d = len(Xrows), Xrows[0].size
+        self.M = Yrows[0].size if Yrows else 0
+        xp = (C.c_void_p * self.N)(*[x.ctypes.data for x in Xrows])
+        yp = (C.c_void_p * self.N)(*[y.ctypes.data for y in Yrows]) if Yrows else None
+        self._ck(self.lib.gprb200_set_train_rows(self.h, xp, self.N, self.d, yp, self.M, float(sigma)))
 
     def set_train_dev(self, dX_ptr, N, d, dY_ptr, M, sigma):
         self.N, self.d, self.M = int(N), int(d), int(M)

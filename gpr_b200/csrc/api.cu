@@ -115,7 +115,12 @@ struct TempBuf {  // stream-ordered scratch
 
 int require(Ctx* c, bool cond, const char* msg) { return cond ? 0 : fail(c, -2, msg); }
 
-int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, int64_t M, double sigma, bool on_device) {
+constexpr int64_t STREAM_IO_MIN_BYTES = 64ll << 20;
+
+// Yrows != nullptr: one host pointer per label vector (the reference's std::vector<VectorType>), Y ignored
+int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, int64_t M, double sigma, bool on_device,
+                  const double* const* Yrows = nullptr) {
+    if (Yrows) Y = Yrows[0];   // "labels present"
     GP_TRY(require(c, N > 0 && d > 0 && X != nullptr, "set_train: need N > 0 samples of dimension d > 0"));
     GP_TRY(require(c, N < (1ll << 31) - 256 && M < (1ll << 31) - 256, "set_train: N and M must fit in 31 bits"));
     // Same shapes as the resident model (the hyper-parameter loop, repeated Learn calls): keep every device buffer.
@@ -134,8 +139,13 @@ int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, in
     if (Y && M > 0) {
         if (!reuse) GP_TRY(dev_alloc(c, &c->dY, (size_t)N * c->ldy));
         if (c->ldy != M) GP_CUDA(c, cudaMemsetAsync(c->dY, 0, sizeof(double) * N * c->ldy, c->stream));
-        GP_CUDA(c, cudaMemcpy2DAsync(c->dY, sizeof(double) * c->ldy, Y, sizeof(double) * M, sizeof(double) * M, N, kind,
-                                     c->stream));
+        const bool big = !on_device && c->opt_stream_io && (int64_t)sizeof(double) * N * M >= STREAM_IO_MIN_BYTES;
+        if (Yrows || big) {
+            GP_TRY(stream_h2d(c, c->dY, c->ldy, Yrows, Yrows ? nullptr : Y, M, N, M));
+        } else {
+            GP_CUDA(c, cudaMemcpy2DAsync(c->dY, sizeof(double) * c->ldy, Y, sizeof(double) * M, sizeof(double) * M, N, kind,
+                                         c->stream));
+        }
     }
     c->have_train = true;
     return 0;
@@ -374,6 +384,7 @@ int gprb200_destroy(gprb200_handle h) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     sparse_destroy(c);
+    hostio_destroy(c);
     free_model(c);
     cudaFree(c->dInfo);
     cudaFree(c->dScratch);
@@ -435,7 +446,7 @@ int gprb200_get_stat(gprb200_handle h, const char* name, double* out) {
 int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
-        {"gram_lower_only", &h->opt_gram_lower_only}, {"gram_terms", &h->opt_gram_terms}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead}, {"chol_left", &h->opt_chol_left},
+        {"gram_lower_only", &h->opt_gram_lower_only}, {"gram_terms", &h->opt_gram_terms}, {"stream_io", &h->opt_stream_io}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead}, {"chol_left", &h->opt_chol_left},
         {"gemm_stages", &h->opt_gemm_stages}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
         {"profile", &h->opt_profile}};
     if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
@@ -481,6 +492,22 @@ int gprb200_set_train(gprb200_handle h, const double* X, int64_t N, int d, const
     GP_TRY(use_device(h));
     GP_TRY(install_train(h, X, N, d, Y, M, sigma, false));
     GP_CUDA(h, cudaStreamSynchronize(h->stream));  // host buffers may be reused by the caller
+    return 0;
+}
+
+int gprb200_set_train_rows(gprb200_handle h, const double* const* Xrows, int64_t N, int d, const double* const* Yrows,
+                           int64_t M, double sigma) {
+    if (!h) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, Xrows != nullptr && N > 0 && d > 0, "set_train_rows: need N > 0 samples of dimension d > 0"));
+    std::vector<double> X((size_t)N * d);   // the samples are small (N x d); only the labels are streamed
+    for (int64_t i = 0; i < N; ++i) {
+        GP_TRY(require(c, Xrows[i] != nullptr && (!Yrows || M <= 0 || Yrows[i] != nullptr), "set_train_rows: null row pointer"));
+        memcpy(X.data() + i * d, Xrows[i], sizeof(double) * d);
+    }
+    GP_TRY(install_train(c, X.data(), N, d, nullptr, M, sigma, false, (Yrows && M > 0) ? Yrows : nullptr));
+    GP_CUDA(c, cudaStreamSynchronize(c->stream));
     return 0;
 }
 
@@ -582,6 +609,8 @@ int gprb200_get_alpha(gprb200_handle h, double* alpha) {
     Ctx* c = h;
     GP_TRY(use_device(c));
     GP_TRY(ensure_alpha(c));
+    if (c->opt_stream_io && (int64_t)sizeof(double) * c->N * c->M >= STREAM_IO_MIN_BYTES)
+        return stream_d2h(c, alpha, c->M, c->dA, c->ldy, c->N, c->M);
     return d2h_2d(c, alpha, c->dA, c->ldy, c->N, c->M);
 }
 

@@ -90,6 +90,12 @@ struct Ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // Predict phase timing (resolved lazily by gprb200_phase_ms)
     bool predict_time_pending = false;
 
+    // pinned staging ring for large host <-> device matrices (hostio.cu)
+    static constexpr int NPIN = 3;
+    void* pin[NPIN] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pin_ev[NPIN] = {nullptr, nullptr, nullptr};
+    int64_t opt_stream_io = 1;   // 1: label / regression matrices >= 64 MB cross PCIe through the pinned ring
+
     void* sparse = nullptr;  // SparseModel (sparse.cu): inducing points and the two m x m factors
     double phase_ms[GPRB200_T_COUNT] = {0};
 };
@@ -155,6 +161,11 @@ int rowdot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, i
 // sparse.cu
 void sparse_invalidate(Ctx* c);
 void sparse_destroy(Ctx* c);
+// hostio.cu: pinned-ring transfers of large matrices; rowptr (one pointer per row) or flat (leading dimension ldf)
+int stream_h2d(Ctx* c, double* dst, int64_t ldd, const double* const* rowptr, const double* flat, int64_t ldf, int64_t rows,
+               int64_t cols);
+int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds, int64_t rows, int64_t cols);
+void hostio_destroy(Ctx* c);
 // predict.cu
 int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out);
 

@@ -8,6 +8,7 @@
 #include <iomanip>
 #include <limits>
 #include <sstream>
+#include <type_traits>
 #include <sys/stat.h>
 
 #include "GaussianProcess.h"
@@ -136,13 +137,25 @@ void GaussianProcess<TScalarType>::SyncModelToDevice() const {
     if (m_TrainDirty) {
         const size_t N = m_SampleVectors.size(), d = m_InputDimension, M = m_OutputDimension;
         if (N == 0) throw std::string("GaussianProcess: no input samples defined");
-        std::vector<double> X(N * d), Y(N * M);
-        for (size_t i = 0; i < N; ++i) {
-            for (size_t k = 0; k < d; ++k) X[i * d + k] = m_SampleVectors[i][k];
-            for (size_t k = 0; k < M; ++k) Y[i * M + k] = m_LabelVectors[i][k];
+        if (std::is_same<TScalarType, double>::value) {
+            // the vectors go to the device from where AddSample left them (one pointer per vector, labels streamed
+            // through pinned staging): no N x M host gather (reference: ComputeLabelMatrixInternal, :621-639)
+            std::vector<const double*> xr(N), yr(N);
+            for (size_t i = 0; i < N; ++i) {
+                xr[i] = reinterpret_cast<const double*>(m_SampleVectors[i].data());
+                yr[i] = M ? reinterpret_cast<const double*>(m_LabelVectors[i].data()) : nullptr;
+            }
+            dev.Check(gprb200_set_train_rows(dev.h, xr.data(), (int64_t)N, (int)d, M ? yr.data() : nullptr, (int64_t)M,
+                                             (double)m_Sigma));
+        } else {
+            std::vector<double> X(N * d), Y(N * M);
+            for (size_t i = 0; i < N; ++i) {
+                for (size_t k = 0; k < d; ++k) X[i * d + k] = m_SampleVectors[i][k];
+                for (size_t k = 0; k < M; ++k) Y[i * M + k] = m_LabelVectors[i][k];
+            }
+            dev.Check(gprb200_set_train(dev.h, X.data(), (int64_t)N, (int)d, M ? Y.data() : nullptr, (int64_t)M,
+                                        (double)m_Sigma));
         }
-        dev.Check(gprb200_set_train(dev.h, X.data(), (int64_t)N, (int)d, M ? Y.data() : nullptr, (int64_t)M,
-                                    (double)m_Sigma));
         dev.sent_sigma = (double)m_Sigma;
         m_TrainDirty = false;
     }

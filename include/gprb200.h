@@ -94,9 +94,17 @@ int gprb200_set_kernel(gprb200_handle h, const int32_t* ops, int nops, const dou
 /* parameters only (hyper-parameter loop, include/GaussianProcessInference.h:90) */
 int gprb200_set_kernel_params(gprb200_handle h, const double* params, int nparams);
 
+
 /* replaces the AoS sample/label lists (lib/GaussianProcess.cpp:36-51) + ComputeLabelMatrix (:621-639)
  * X: N x d, Y: N x M, sigma: observation noise (SetSigma). Copies; invalidates any factorisation. */
 int gprb200_set_train(gprb200_handle h, const double* X, int64_t N, int d, const double* Y, int64_t M, double sigma);
+/* The same from the reference's own storage, std::vector<VectorType> (lib/GaussianProcess.cpp:48-49): one host pointer
+ * per sample (d doubles) and per label vector (M doubles). The label rows are streamed through a ring of pinned
+ * staging buffers (worker threads fill piece k+1 while piece k crosses PCIe), so ComputeLabelMatrixInternal's
+ * N x M gather (:621-639; 25.8 GB at N = 4096, M = 786432) never exists on the host. gprb200_set_train with a
+ * contiguous Y >= 64 MB and gprb200_get_alpha use the same pipeline (option "stream_io" = 0 turns it off). */
+int gprb200_set_train_rows(gprb200_handle h, const double* const* Xrows, int64_t N, int d, const double* const* Yrows,
+                           int64_t M, double sigma);
 int gprb200_set_train_dev(gprb200_handle h, const double* dX, int64_t N, int d, const double* dY, int64_t M,
                           double sigma);
 int gprb200_set_sigma(gprb200_handle h, double sigma);
