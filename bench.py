@@ -633,6 +633,18 @@ def run_host_io(torch, gpr_b200, local_rank, N=4096, d=30, M=196608):
     t0 = time.perf_counter()
     h._ck(h.lib.gprb200_get_alpha(h.h, A.ctypes.data))
     out["alpha_to_host_s"] = time.perf_counter() - t0
+    # Learn end to end (host vectors -> host alpha): three steps one after the other, then pipelined over column blocks
+    t0 = time.perf_counter()
+    h.set_train_rows(xr, rows, C2_SIGMA)
+    h.learn(0)
+    h._ck(h.lib.gprb200_get_alpha(h.h, A.ctypes.data))
+    out["learn_e2e_sequential_s"] = time.perf_counter() - t0
+    h.learn_rows(xr, rows, C2_SIGMA, A)       # warm-up: copy streams, second pinned ring
+    t0 = time.perf_counter()
+    h.learn_rows(xr, rows, C2_SIGMA, A)
+    out["learn_e2e_pipelined_s"] = time.perf_counter() - t0
+    out["learn_e2e_note"] = ("host label vectors -> Gram + Cholesky + solve of all %d columns -> host regression vectors; "
+                             "pipelined = gprb200_learn_rows (upload, solve, download overlapped on three streams)" % M)
     h.set_option("stream_io", 0)
     t0 = time.perf_counter()
     Y = np.empty((N, M))

@@ -57,6 +57,7 @@ _PROTOS = {
     "gprb200_dgram": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_loglik": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gprb200_quadform": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "gprb200_learn_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_double, C.c_void_p]),
     "gprb200_set_train_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_double]),
     "gprb200_sparse_set_inducing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double]),
     "gprb200_sparse_set_jitter": (C.c_int, [C.c_void_p, C.c_double]),
@@ -182,6 +183,16 @@ class Handle:
         xp = (C.c_void_p * self.N)(*[x.ctypes.data for x in Xrows])
         yp = (C.c_void_p * self.N)(*[y.ctypes.data for y in Yrows]) if Yrows else None
         self._ck(self.lib.gprb200_set_train_rows(self.h, xp, self.N, self.d, yp, self.M, float(sigma)))
+
+    def learn_rows(self, Xrows, Yrows, sigma, alpha_out=None):
+        """pipelined AddSample x N + Initialize (+ host copy of alpha): upload, solve and download in column blocks"""
+        Xrows = [_f64(x).ravel() for x in Xrows]
+        Yrows = [_f64(y).ravel() for y in Yrows]
+        self.N, self.d, self.M = len(Xrows), Xrows[0].size, Yrows[0].size
+        xp = (C.c_void_p * self.N)(*[x.ctypes.data for x in Xrows])
+        yp = (C.c_void_p * self.N)(*[y.ctypes.data for y in Yrows])
+        self._ck(self.lib.gprb200_learn_rows(self.h, xp, self.N, self.d, yp, self.M, float(sigma), _ptr(alpha_out)))
+        return alpha_out
 
     def set_train_dev(self, dX_ptr, N, d, dY_ptr, M, sigma):
         self.N, self.d, self.M = int(N), int(d), int(M)

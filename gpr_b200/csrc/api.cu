@@ -10,6 +10,8 @@
 #include <string.h>
 #include <vector>
 #include <new>
+#include <atomic>
+#include <thread>
 
 using namespace gprb200;
 
@@ -118,8 +120,9 @@ int require(Ctx* c, bool cond, const char* msg) { return cond ? 0 : fail(c, -2, 
 constexpr int64_t STREAM_IO_MIN_BYTES = 64ll << 20;
 
 // Yrows != nullptr: one host pointer per label vector (the reference's std::vector<VectorType>), Y ignored
+// defer_labels: allocate the label matrix but leave the upload to the caller (gprb200_learn_rows streams it in column blocks)
 int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, int64_t M, double sigma, bool on_device,
-                  const double* const* Yrows = nullptr) {
+                  const double* const* Yrows = nullptr, bool defer_labels = false) {
     if (Yrows) Y = Yrows[0];   // "labels present"
     GP_TRY(require(c, N > 0 && d > 0 && X != nullptr, "set_train: need N > 0 samples of dimension d > 0"));
     GP_TRY(require(c, N < (1ll << 31) - 256 && M < (1ll << 31) - 256, "set_train: N and M must fit in 31 bits"));
@@ -140,7 +143,8 @@ int install_train(Ctx* c, const double* X, int64_t N, int d, const double* Y, in
         if (!reuse) GP_TRY(dev_alloc(c, &c->dY, (size_t)N * c->ldy));
         if (c->ldy != M) GP_CUDA(c, cudaMemsetAsync(c->dY, 0, sizeof(double) * N * c->ldy, c->stream));
         const bool big = !on_device && c->opt_stream_io && (int64_t)sizeof(double) * N * M >= STREAM_IO_MIN_BYTES;
-        if (Yrows || big) {
+        if (defer_labels) {
+        } else if (Yrows || big) {
             GP_TRY(stream_h2d(c, c->dY, c->ldy, Yrows, Yrows ? nullptr : Y, M, N, M));
         } else {
             GP_CUDA(c, cudaMemcpy2DAsync(c->dY, sizeof(double) * c->ldy, Y, sizeof(double) * M, sizeof(double) * M, N, kind,
@@ -508,6 +512,105 @@ int gprb200_set_train_rows(gprb200_handle h, const double* const* Xrows, int64_t
     }
     GP_TRY(install_train(c, X.data(), N, d, nullptr, M, sigma, false, (Yrows && M > 0) ? Yrows : nullptr));
     GP_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// Learn straight from the reference's storage to the host result, pipelined over column blocks of the label matrix:
+//   uploader thread : label rows -> pinned ring 0 -> dY block            (copy stream 0)
+//   this thread     : K = LL^T once, then per block  alpha_b = L^-T L^-1 Y_b    (compute stream)
+//   downloader thread: alpha block -> pinned ring 1 -> alpha_out           (copy stream 1)
+// The output columns are independent (lib/GaussianProcess.cpp:661 is one GEMM over all of them), so block b+1 crosses
+// PCIe one way and block b-1 the other way while block b is solved; Y and alpha stay resident for Predict.
+int gprb200_learn_rows(gprb200_handle h, const double* const* Xrows, int64_t N, int d, const double* const* Yrows, int64_t M,
+                       double sigma, double* alpha_out) {
+    if (!h) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, Xrows && Yrows && N > 0 && d > 0 && M > 0, "learn_rows: need samples and label vectors"));
+    std::vector<double> X((size_t)N * d);
+    for (int64_t i = 0; i < N; ++i) {
+        GP_TRY(require(c, Xrows[i] != nullptr && Yrows[i] != nullptr, "learn_rows: null row pointer"));
+        memcpy(X.data() + i * d, Xrows[i], sizeof(double) * d);
+    }
+    GP_TRY(install_train(c, X.data(), N, d, nullptr, M, sigma, false, Yrows, true));
+    for (int r = 0; r < 2; ++r)
+        if (!c->io_stream[r]) GP_CUDA(c, cudaStreamCreateWithFlags(&c->io_stream[r], cudaStreamNonBlocking));
+    if (!c->dA) GP_TRY(dev_alloc(c, &c->dA, (size_t)N * c->ldy));
+    // column blocks of ~512 MB
+    int64_t wc = ((512ll << 20) / (8 * N)) / 16 * 16;
+    if (wc < 16) wc = 16;
+    if (wc > M) wc = M;
+    const int64_t B = (M + wc - 1) / wc;
+    std::vector<cudaEvent_t> evU((size_t)B), evS((size_t)B);
+    for (int64_t b = 0; b < B; ++b) {
+        GP_CUDA(c, cudaEventCreateWithFlags(&evU[(size_t)b], cudaEventDisableTiming));
+        GP_CUDA(c, cudaEventCreateWithFlags(&evS[(size_t)b], cudaEventDisableTiming));
+    }
+    std::atomic<int64_t> uploaded(0), solved(0);
+    std::atomic<int> rc_up(0), rc_down(0);
+    GP_CUDA(c, cudaStreamSynchronize(c->stream));   // dY allocated and padded before the copy stream writes into it
+    std::thread up([&] {
+        cudaSetDevice(c->device);
+        for (int64_t b = 0; b < B; ++b) {
+            const int64_t c0 = b * wc, w = (M - c0 < wc) ? M - c0 : wc;
+            int r = stream_h2d(c, c->dY + c0, c->ldy, Yrows, nullptr, 0, N, w, c->io_stream[0], c0);
+            if (r == 0 && cudaEventRecord(evU[(size_t)b], c->io_stream[0]) != cudaSuccess) r = -1;
+            if (r != 0) {
+                rc_up.store(r);
+                uploaded.store(B);   // unblock the solver; it checks rc_up
+                return;
+            }
+            uploaded.store(b + 1);
+        }
+    });
+    std::thread down([&] {
+        cudaSetDevice(c->device);
+        if (!alpha_out) return;
+        for (int64_t b = 0; b < B; ++b) {
+            while (solved.load() <= b) std::this_thread::yield();
+            if (solved.load() > B) return;   // the solver failed
+            const int64_t c0 = b * wc, w = (M - c0 < wc) ? M - c0 : wc;
+            int r = (cudaStreamWaitEvent(c->io_stream[1], evS[(size_t)b], 0) == cudaSuccess) ? 0 : -1;
+            if (r == 0) r = stream_d2h(c, alpha_out + c0, M, c->dA + c0, c->ldy, N, w, c->io_stream[1]);
+            if (r != 0) {
+                rc_down.store(r);
+                return;
+            }
+        }
+    });
+    int rc = ensure_factor(c);   // Gram + Cholesky while the first block is on its way
+    for (int64_t b = 0; b < B && rc == 0; ++b) {
+        while (uploaded.load() <= b) std::this_thread::yield();
+        if (rc_up.load() != 0) {
+            rc = rc_up.load();
+            break;
+        }
+        const int64_t c0 = b * wc, w = (M - c0 < wc) ? M - c0 : wc;
+        if (cudaStreamWaitEvent(c->stream, evU[(size_t)b], 0) != cudaSuccess ||
+            cudaMemcpy2DAsync(c->dA + c0, sizeof(double) * c->ldy, c->dY + c0, sizeof(double) * c->ldy, sizeof(double) * w,
+                              (size_t)N, cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) {
+            rc = fail(c, -1, "learn_rows: CUDA error while staging a label block");
+            break;
+        }
+        rc = trsm_lower_fwd(c, c->dL, c->ldk, c->dInvL, N, c->dA + c0, c->ldy, w);
+        if (rc == 0) rc = trsm_lower_bwd(c, c->dL, c->ldk, c->dInvL, N, c->dA + c0, c->ldy, w);
+        if (rc == 0 && cudaEventRecord(evS[(size_t)b], c->stream) != cudaSuccess) rc = fail(c, -1, "learn_rows: event record failed");
+        if (rc == 0) solved.store(b + 1);
+    }
+    if (rc != 0) solved.store(B + 1);   // release the downloader
+    up.join();
+    down.join();
+    cudaStreamSynchronize(c->io_stream[0]);
+    cudaStreamSynchronize(c->io_stream[1]);
+    cudaStreamSynchronize(c->stream);
+    for (int64_t b = 0; b < B; ++b) {
+        cudaEventDestroy(evU[(size_t)b]);
+        cudaEventDestroy(evS[(size_t)b]);
+    }
+    if (rc == 0 && rc_up.load() != 0) rc = rc_up.load();
+    if (rc == 0 && rc_down.load() != 0) rc = rc_down.load();
+    if (rc != 0) return rc;
+    c->have_alpha = true;
     return 0;
 }
 

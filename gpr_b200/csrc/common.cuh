@@ -92,8 +92,9 @@ struct Ctx {
 
     // pinned staging ring for large host <-> device matrices (hostio.cu)
     static constexpr int NPIN = 3;
-    void* pin[NPIN] = {nullptr, nullptr, nullptr};
-    cudaEvent_t pin_ev[NPIN] = {nullptr, nullptr, nullptr};
+    void* pin[2][NPIN] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // ring 0: to device, ring 1: to host
+    cudaEvent_t pin_ev[2][NPIN] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+    cudaStream_t io_stream[2] = {nullptr, nullptr};   // copy streams of the pipelined Learn (gprb200_learn_rows)
     int64_t opt_stream_io = 1;   // 1: label / regression matrices >= 64 MB cross PCIe through the pinned ring
 
     void* sparse = nullptr;  // SparseModel (sparse.cu): inducing points and the two m x m factors
@@ -162,9 +163,11 @@ int rowdot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, i
 void sparse_invalidate(Ctx* c);
 void sparse_destroy(Ctx* c);
 // hostio.cu: pinned-ring transfers of large matrices; rowptr (one pointer per row) or flat (leading dimension ldf)
+// st == nullptr: c->stream. hoff: column offset applied to every host row (a column block of a wider host matrix).
 int stream_h2d(Ctx* c, double* dst, int64_t ldd, const double* const* rowptr, const double* flat, int64_t ldf, int64_t rows,
-               int64_t cols);
-int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds, int64_t rows, int64_t cols);
+               int64_t cols, cudaStream_t st = nullptr, int64_t hoff = 0);
+int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds, int64_t rows, int64_t cols,
+               cudaStream_t st = nullptr);
 void hostio_destroy(Ctx* c);
 // predict.cu
 int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out);

@@ -19,10 +19,10 @@ namespace {
 constexpr size_t PIECE_BYTES = 64u << 20;   // one staging buffer
 constexpr int NTHREADS = 8;                 // copy workers per piece
 
-int ensure_pinned(Ctx* c) {
+int ensure_pinned(Ctx* c, int ring) {
     for (int k = 0; k < Ctx::NPIN; ++k) {
-        if (!c->pin[k]) GP_CUDA(c, cudaHostAlloc(&c->pin[k], PIECE_BYTES, cudaHostAllocDefault));
-        if (!c->pin_ev[k]) GP_CUDA(c, cudaEventCreateWithFlags(&c->pin_ev[k], cudaEventDisableTiming));
+        if (!c->pin[ring][k]) GP_CUDA(c, cudaHostAlloc(&c->pin[ring][k], PIECE_BYTES, cudaHostAllocDefault));
+        if (!c->pin_ev[ring][k]) GP_CUDA(c, cudaEventCreateWithFlags(&c->pin_ev[ring][k], cudaEventDisableTiming));
     }
     return 0;
 }
@@ -80,35 +80,42 @@ void copy_piece(const Piece& p, double* buf, const double* const* rowptr, const 
 }  // namespace
 
 // dst (device, rows x cols, leading dimension ldd) <- host rows; rowptr (one pointer per row) or flat (leading
-// dimension ldf). Asynchronous on c->stream except for the staging-buffer reuse waits; the caller synchronises.
+// dimension ldf), each read from column hoff. Asynchronous on st except for the staging-buffer reuse waits; the
+// caller synchronises. Ring 0.
 int stream_h2d(Ctx* c, double* dst, int64_t ldd, const double* const* rowptr, const double* flat, int64_t ldf, int64_t rows,
-               int64_t cols) {
+               int64_t cols, cudaStream_t st, int64_t hoff) {
     if (rows <= 0 || cols <= 0) return 0;
-    GP_TRY(ensure_pinned(c));
+    if (!st) st = c->stream;
+    GP_TRY(ensure_pinned(c, 0));
+    // a previous call may still be reading the ring (its copies are asynchronous)
+    for (int k = 0; k < Ctx::NPIN; ++k) GP_CUDA(c, cudaEventSynchronize(c->pin_ev[0][k]));
     const std::vector<Piece> ps = pieces(rows, cols);
     for (size_t k = 0; k < ps.size(); ++k) {
         const int b = (int)(k % Ctx::NPIN);
-        if (k >= (size_t)Ctx::NPIN) GP_CUDA(c, cudaEventSynchronize(c->pin_ev[b]));   // its previous upload has left the buffer
-        const Piece& p = ps[k];
-        copy_piece(p, (double*)c->pin[b], rowptr, flat, ldf, true);
-        GP_CUDA(c, cudaMemcpy2DAsync(dst + p.r0 * ldd + p.c0, sizeof(double) * ldd, c->pin[b], sizeof(double) * p.nc,
-                                     sizeof(double) * p.nc, (size_t)p.nr, cudaMemcpyHostToDevice, c->stream));
-        GP_CUDA(c, cudaEventRecord(c->pin_ev[b], c->stream));
+        if (k >= (size_t)Ctx::NPIN) GP_CUDA(c, cudaEventSynchronize(c->pin_ev[0][b]));   // its previous upload has left the buffer
+        Piece p = ps[k];
+        p.c0 += hoff;
+        copy_piece(p, (double*)c->pin[0][b], rowptr, flat, ldf, true);
+        GP_CUDA(c, cudaMemcpy2DAsync(dst + p.r0 * ldd + ps[k].c0, sizeof(double) * ldd, c->pin[0][b], sizeof(double) * p.nc,
+                                     sizeof(double) * p.nc, (size_t)p.nr, cudaMemcpyHostToDevice, st));
+        GP_CUDA(c, cudaEventRecord(c->pin_ev[0][b], st));
     }
     return 0;
 }
 
 // host (flat, leading dimension ldf) <- src (device, rows x cols, leading dimension lds); returns when the host has it
-int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds, int64_t rows, int64_t cols) {
+int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds, int64_t rows, int64_t cols,
+               cudaStream_t st) {
     if (rows <= 0 || cols <= 0) return 0;
-    GP_TRY(ensure_pinned(c));
+    if (!st) st = c->stream;
+    GP_TRY(ensure_pinned(c, 1));
     const std::vector<Piece> ps = pieces(rows, cols);
     auto issue = [&](size_t k) -> int {
         const int b = (int)(k % Ctx::NPIN);
         const Piece& p = ps[k];
-        GP_CUDA(c, cudaMemcpy2DAsync(c->pin[b], sizeof(double) * p.nc, src + p.r0 * lds + p.c0, sizeof(double) * lds,
-                                     sizeof(double) * p.nc, (size_t)p.nr, cudaMemcpyDeviceToHost, c->stream));
-        GP_CUDA(c, cudaEventRecord(c->pin_ev[b], c->stream));
+        GP_CUDA(c, cudaMemcpy2DAsync(c->pin[1][b], sizeof(double) * p.nc, src + p.r0 * lds + p.c0, sizeof(double) * lds,
+                                     sizeof(double) * p.nc, (size_t)p.nr, cudaMemcpyDeviceToHost, st));
+        GP_CUDA(c, cudaEventRecord(c->pin_ev[1][b], st));
         return 0;
     };
     const size_t ahead = Ctx::NPIN - 1;   // downloads in flight while the host empties a buffer
@@ -116,18 +123,22 @@ int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds
     for (size_t k = 0; k < ps.size(); ++k) {
         if (k + ahead < ps.size()) GP_TRY(issue(k + ahead));
         const int b = (int)(k % Ctx::NPIN);
-        GP_CUDA(c, cudaEventSynchronize(c->pin_ev[b]));
-        copy_piece(ps[k], (double*)c->pin[b], nullptr, flat, ldf, false);
+        GP_CUDA(c, cudaEventSynchronize(c->pin_ev[1][b]));
+        copy_piece(ps[k], (double*)c->pin[1][b], nullptr, flat, ldf, false);
     }
     return 0;
 }
 
 void hostio_destroy(Ctx* c) {
-    for (int k = 0; k < Ctx::NPIN; ++k) {
-        if (c->pin[k]) cudaFreeHost(c->pin[k]);
-        if (c->pin_ev[k]) cudaEventDestroy(c->pin_ev[k]);
-        c->pin[k] = nullptr;
-        c->pin_ev[k] = nullptr;
+    for (int r = 0; r < 2; ++r) {
+        for (int k = 0; k < Ctx::NPIN; ++k) {
+            if (c->pin[r][k]) cudaFreeHost(c->pin[r][k]);
+            if (c->pin_ev[r][k]) cudaEventDestroy(c->pin_ev[r][k]);
+            c->pin[r][k] = nullptr;
+            c->pin_ev[r][k] = nullptr;
+        }
+        if (c->io_stream[r]) cudaStreamDestroy(c->io_stream[r]);
+        c->io_stream[r] = nullptr;
     }
 }
 

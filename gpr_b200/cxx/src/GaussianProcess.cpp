@@ -194,9 +194,32 @@ void GaussianProcess<TScalarType>::Initialize() {
 // reference :642-672 — Gram + noise, factor, alpha; C is not formed here (see MirrorCoreMatrix)
 template <class TScalarType>
 void GaussianProcess<TScalarType>::ComputeRegressionVectors() {
-    SyncModelToDevice();
-    detail::DeviceModel& dev = Device();
-    dev.Check(gprb200_learn(dev.h, 0u));
+    const size_t N0 = m_SampleVectors.size(), M0 = m_OutputDimension;
+    if (std::is_same<TScalarType, double>::value && m_TrainDirty && N0 * M0 * sizeof(double) >= (size_t(64) << 20)) {
+        // large label matrix: upload and solve overlapped over column blocks, straight from the AddSample storage
+        m_TrainDirty = false;    // SyncModelToDevice below only brings the kernel up to date
+        try {
+            SyncModelToDevice();
+        } catch (...) {
+            m_TrainDirty = true;
+            throw;
+        }
+        detail::DeviceModel& dev = Device();
+        std::vector<const double*> xr(N0), yr(N0);
+        for (size_t i = 0; i < N0; ++i) {
+            xr[i] = reinterpret_cast<const double*>(m_SampleVectors[i].data());
+            yr[i] = reinterpret_cast<const double*>(m_LabelVectors[i].data());
+        }
+        m_TrainDirty = true;     // restored if the call throws
+        dev.Check(gprb200_learn_rows(dev.h, xr.data(), (int64_t)N0, (int)m_InputDimension, yr.data(), (int64_t)M0,
+                                     (double)m_Sigma, nullptr));
+        dev.sent_sigma = (double)m_Sigma;
+        m_TrainDirty = false;
+    } else {
+        SyncModelToDevice();
+        detail::DeviceModel& dev = Device();
+        dev.Check(gprb200_learn(dev.h, 0u));
+    }
     m_AlphaMirrored = false;
     m_CoreMirrored = false;
     m_RegressionVectors.resize(0, 0);

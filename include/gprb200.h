@@ -105,6 +105,13 @@ int gprb200_set_train(gprb200_handle h, const double* X, int64_t N, int d, const
  * contiguous Y >= 64 MB and gprb200_get_alpha use the same pipeline (option "stream_io" = 0 turns it off). */
 int gprb200_set_train_rows(gprb200_handle h, const double* const* Xrows, int64_t N, int d, const double* const* Yrows,
                            int64_t M, double sigma);
+/* AddSample x N + Initialize (+ the host copy of the regression vectors that Save and operator== need) in one pipelined
+ * call: label vectors are uploaded, solved and downloaded in column blocks of ~512 MB on three streams, so at
+ * N = 4096, M = 786432 the 25.8 GB each way overlap the solve instead of adding to it. alpha_out: N x M host buffer
+ * or NULL (alpha then stays on the device only). Equivalent to set_train_rows + learn + get_alpha (to rounding: a narrow last block may take a differently
+ * ordered triangular solve). */
+int gprb200_learn_rows(gprb200_handle h, const double* const* Xrows, int64_t N, int d, const double* const* Yrows, int64_t M,
+                       double sigma, double* alpha_out);
 int gprb200_set_train_dev(gprb200_handle h, const double* dX, int64_t N, int d, const double* dY, int64_t M,
                           double sigma);
 int gprb200_set_sigma(gprb200_handle h, double sigma);

@@ -226,6 +226,35 @@ int main() {
             EXPECT(mean.rows() == T && mean.cols() == 5 && ci.rows() == T, "T7 batch shapes");
             EXPECT(worst_mean < 1e-12 && worst_ci < 1e-9, "T7 PredictBatch equals the one-point calls");
         }
+        // ---- T8: label matrix >= 64 MB: Initialize takes the pipelined path (gprb200_learn_rows) -----------------
+        {
+            const unsigned N = 96, M = 100003;     // 76.8 MB of labels
+            GP::Pointer big(new GP(Kernel<double>::Pointer(new GaussianKernel<double>(1.3, 1.0))));
+            GP::Pointer one(new GP(Kernel<double>::Pointer(new GaussianKernel<double>(1.3, 1.0))));
+            big->SetSigma(0.4);
+            one->SetSigma(0.4);
+            const unsigned probe = 77777;
+            for (unsigned i = 0; i < N; ++i) {
+                Vec x(2), y(M), y1(1);
+                x[0] = std::sin(0.37 * i);
+                x[1] = std::cos(0.11 * i * i);
+                for (unsigned k = 0; k < M; ++k) y[k] = std::sin(x[0] * (1 + k % 13)) + 1e-3 * (k % 101) * x[1];
+                y1[0] = y[probe];
+                big->AddSample(x, y);
+                one->AddSample(x, y1);
+            }
+            Vec xs(2);
+            xs[0] = 0.21;
+            xs[1] = -0.4;
+            const Vec yb = big->Predict(xs);
+            const Vec y1 = one->Predict(xs);
+            EXPECT(yb.rows() == (long)M && std::fabs(yb[probe] - y1[0]) < 1e-11 * (1 + std::fabs(y1[0])),
+                   "T8 pipelined Initialize: column of the 100003-column model equals the single-column model");
+            big->Save("/tmp/gprb200_T8");
+            GP::Pointer back(new GP(Kernel<double>::Pointer(new WhiteKernel<double>(1.0))));
+            back->Load("/tmp/gprb200_T8");
+            EXPECT(std::fabs(back->Predict(xs)[probe] - yb[probe]) < 1e-13, "T8 Save / Load of the large model");
+        }
     } catch (std::string& s) {
         std::cout << "[failed] exception: " << s << std::endl;
         return -1;

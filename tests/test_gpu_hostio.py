@@ -44,3 +44,29 @@ def test_row_pointer_form_on_a_small_problem_and_errors():
     h.set_train_rows([x for x in X], None, 0.5)                        # samples only (no labels)
     assert h.kernel_vector(X[:2]).shape == (2, 40)
     h.close()
+
+
+def test_pipelined_learn_rows_equals_the_three_step_path():
+    """gprb200_learn_rows (upload / solve / download overlapped over column blocks) against set_train + learn +
+    get_alpha: three blocks of 32768 columns at N = 2048, the last one ragged; Predict afterwards uses the resident alpha."""
+    import gpr_b200
+    rng = np.random.default_rng(77)
+    N, M = 2048, 70001
+    X = rng.uniform(-1, 1, (N, 3))
+    Y = rng.standard_normal((N, M))
+    ref = _learned(X, Y, stream=0)
+    h = gpr_b200.Handle(0)
+    h.set_kernel(*gpr_b200.GaussianKernel(1.5, 1.0).lower())
+    A = np.empty((N, M))
+    h.learn_rows([x for x in X], [y.copy() for y in Y], 0.5, A)
+    # same factor, same algorithm; a narrow last block takes the right-looking instead of the left-looking triangular
+    # solve (solve.cu), so the sums are ordered differently: agreement to rounding, not bit for bit
+    scale = np.abs(ref).max()
+    assert np.abs(A - ref).max() <= 1e-12 * scale
+    assert np.array_equal(A[:, :65536], ref[:, :65536])         # full-width blocks take the same path: identical
+    assert np.array_equal(h.alpha(), A)                         # the device copy is complete as well
+    mean = h.predict(X[:3])
+    assert np.abs(mean - (Y[:3] - 0.25 * ref[:3])).max() <= 1e-9 * np.abs(Y).max()
+    h.learn_rows([x for x in X], [y.copy() for y in Y], 0.5, None)   # no host copy requested
+    assert np.array_equal(h.alpha(), A)
+    h.close()
