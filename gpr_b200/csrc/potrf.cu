@@ -184,15 +184,18 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
                 for (int i = 0; i < P2_IB; ++i) {
                     const double* Li = S + (c0 + i) * P2_LD + c0;
                     const double ri = rdb[i];
-                    double acc0 = 0.0, acc1 = 0.0;  // two chains halve the dependent FMA latency
+                    // four chains: a dependent DFMA costs ~40 cycles on sm_100 (tools/fp64_probe.cu)
+                    double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
                     for (int k = 0; k < i; ++k) {
                         if (k >= lane) {
-                            if (k & 1) acc1 = fma(Li[k], w[k], acc1);
-                            else acc0 = fma(Li[k], w[k], acc0);
+                            if ((k & 3) == 0) acc0 = fma(Li[k], w[k], acc0);
+                            else if ((k & 3) == 1) acc1 = fma(Li[k], w[k], acc1);
+                            else if ((k & 3) == 2) acc2 = fma(Li[k], w[k], acc2);
+                            else acc3 = fma(Li[k], w[k], acc3);
                         }
                     }
-                    w[i] = (i == lane) ? ri : ((i > lane) ? -(acc0 + acc1) * ri : 0.0);
+                    w[i] = (i == lane) ? ri : ((i > lane) ? -((acc0 + acc1) + (acc2 + acc3)) * ri : 0.0);
                 }
 #pragma unroll
                 for (int i = 0; i < P2_IB; ++i) Wd[(b * P2_IB + i) * (P2_IB + 1) + lane] = w[i];
@@ -210,10 +213,15 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
             for (int k = 0; k < P2_IB; ++k) wrow[k] = Wb[lane * (P2_IB + 1) + k];  // W[j = lane][k], zero for k > j
             for (int r = r0 + warp; r < NB; r += WARPS) {
                 const double v = S[r * P2_LD + c0 + lane];
-                double x = 0.0;
+                double x0 = 0.0, x1 = 0.0, x2 = 0.0, x3 = 0.0;   // four independent chains (DFMA latency)
 #pragma unroll
-                for (int k = 0; k < P2_IB; ++k) x = fma(__shfl_sync(FULL, v, k), wrow[k], x);
-                S[r * P2_LD + c0 + lane] = x;
+                for (int k = 0; k < P2_IB; k += 4) {
+                    x0 = fma(__shfl_sync(FULL, v, k), wrow[k], x0);
+                    x1 = fma(__shfl_sync(FULL, v, k + 1), wrow[k + 1], x1);
+                    x2 = fma(__shfl_sync(FULL, v, k + 2), wrow[k + 2], x2);
+                    x3 = fma(__shfl_sync(FULL, v, k + 3), wrow[k + 3], x3);
+                }
+                S[r * P2_LD + c0 + lane] = (x0 + x1) + (x2 + x3);
             }
         }
         __syncthreads();
@@ -225,10 +233,15 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
             for (int k = 0; k < P2_IB; ++k) colv[k] = S[c * P2_LD + c0 + k];
             for (int r = cc + warp; r < NB; r += WARPS) {  // rows >= cc; entries with c > r are skipped
                 const double* xr = S + r * P2_LD + c0;
-                double acc = 0.0;
+                double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
-                for (int k = 0; k < P2_IB; ++k) acc = fma(xr[k], colv[k], acc);
-                if (c <= r) S[r * P2_LD + c] -= acc;
+                for (int k = 0; k < P2_IB; k += 4) {
+                    a0 = fma(xr[k], colv[k], a0);
+                    a1 = fma(xr[k + 1], colv[k + 1], a1);
+                    a2 = fma(xr[k + 2], colv[k + 2], a2);
+                    a3 = fma(xr[k + 3], colv[k + 3], a3);
+                }
+                if (c <= r) S[r * P2_LD + c] -= (a0 + a1) + (a2 + a3);
             }
         }
         __syncthreads();
@@ -249,20 +262,30 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
             const int p = o / (P2_IB * P2_IB), rc = o - p * P2_IB * P2_IB;
             const int r = rc / P2_IB, c = rc - r * P2_IB;
             const int i = dist + p, j = p;
-            double acc = 0.0;
+            double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;   // four chains
             for (int k = j; k < i; ++k) {
                 const double* Lik = S + (P2_IB * i + r) * P2_LD + P2_IB * k;
                 if (k == j) {
                     const double* Wjj = Wd + j * P2_IB * (P2_IB + 1);
-#pragma unroll 8
-                    for (int t = 0; t < P2_IB; ++t) acc = fma(Lik[t], Wjj[t * (P2_IB + 1) + c], acc);
+#pragma unroll
+                    for (int t = 0; t < P2_IB; t += 4) {
+                        b0 = fma(Lik[t], Wjj[t * (P2_IB + 1) + c], b0);
+                        b1 = fma(Lik[t + 1], Wjj[(t + 1) * (P2_IB + 1) + c], b1);
+                        b2 = fma(Lik[t + 2], Wjj[(t + 2) * (P2_IB + 1) + c], b2);
+                        b3 = fma(Lik[t + 3], Wjj[(t + 3) * (P2_IB + 1) + c], b3);
+                    }
                 } else {
                     const double* Wkj = S + (P2_IB * j + c) * P2_LD + P2_IB * k;  // transposed storage
-#pragma unroll 8
-                    for (int t = 0; t < P2_IB; ++t) acc = fma(Lik[t], Wkj[t], acc);
+#pragma unroll
+                    for (int t = 0; t < P2_IB; t += 4) {
+                        b0 = fma(Lik[t], Wkj[t], b0);
+                        b1 = fma(Lik[t + 1], Wkj[t + 1], b1);
+                        b2 = fma(Lik[t + 2], Wkj[t + 2], b2);
+                        b3 = fma(Lik[t + 3], Wkj[t + 3], b3);
+                    }
                 }
             }
-            Tm[(p * P2_IB + r) * (P2_IB + 1) + c] = acc;
+            Tm[(p * P2_IB + r) * (P2_IB + 1) + c] = (b0 + b1) + (b2 + b3);
         }
         __syncthreads();
         // W_ij = -W_ii T
@@ -272,10 +295,15 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
             const int i = dist + p, j = p;
             const double* Wii = Wd + i * P2_IB * (P2_IB + 1);
             const double* T = Tm + p * P2_IB * (P2_IB + 1);
-            double acc = 0.0;
-#pragma unroll 8
-            for (int t = 0; t < P2_IB; ++t) acc = fma(Wii[r * (P2_IB + 1) + t], T[t * (P2_IB + 1) + c], acc);  // W_ii[r][t] = 0 for t > r
-            S[(P2_IB * j + c) * P2_LD + P2_IB * i + r] = -acc;
+            double d0 = 0.0, d1 = 0.0, d2 = 0.0, d3 = 0.0;
+#pragma unroll
+            for (int t = 0; t < P2_IB; t += 4) {   // W_ii[r][t] = 0 for t > r
+                d0 = fma(Wii[r * (P2_IB + 1) + t], T[t * (P2_IB + 1) + c], d0);
+                d1 = fma(Wii[r * (P2_IB + 1) + t + 1], T[(t + 1) * (P2_IB + 1) + c], d1);
+                d2 = fma(Wii[r * (P2_IB + 1) + t + 2], T[(t + 2) * (P2_IB + 1) + c], d2);
+                d3 = fma(Wii[r * (P2_IB + 1) + t + 3], T[(t + 3) * (P2_IB + 1) + c], d3);
+            }
+            S[(P2_IB * j + c) * P2_LD + P2_IB * i + r] = -((d0 + d1) + (d2 + d3));
         }
         __syncthreads();
     }
