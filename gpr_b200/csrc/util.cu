@@ -48,6 +48,41 @@ __global__ void coldot_kernel(const double* A, int64_t lda, const double* B, int
     for (int64_t r = 0; r < rows; ++r) s = fma(A[r * lda + c], B[r * ldb + c], s);
     out[c] = s;
 }
+// Few columns, many rows (the quadratic form y^T alpha at M = 1: one thread would walk all N rows): rows split into
+// chunks over blockIdx.y and over the 8 row lanes of a 32 x 8 block; partial sums [chunk][col] are then added in chunk
+// order by coldot_finish_kernel, so the result does not depend on scheduling.
+constexpr int CD_ROWS_PER_CHUNK = 512;
+__global__ void coldot_part_kernel(const double* A, int64_t lda, const double* B, int64_t ldb, int64_t rows, int64_t cols,
+                                   double* part) {
+    __shared__ double red[8][33];
+    const int64_t c = (int64_t)blockIdx.x * 32 + threadIdx.x;
+    const int64_t r0 = (int64_t)blockIdx.y * CD_ROWS_PER_CHUNK;
+    const int64_t r1 = (r0 + CD_ROWS_PER_CHUNK < rows) ? r0 + CD_ROWS_PER_CHUNK : rows;
+    double s0 = 0.0, s1 = 0.0;
+    if (c < cols) {
+        int64_t r = r0 + threadIdx.y;
+        for (; r + 8 < r1; r += 16) {
+            s0 = fma(A[r * lda + c], B[r * ldb + c], s0);
+            s1 = fma(A[(r + 8) * lda + c], B[(r + 8) * ldb + c], s1);
+        }
+        if (r < r1) s0 = fma(A[r * lda + c], B[r * ldb + c], s0);
+    }
+    red[threadIdx.y][threadIdx.x] = s0 + s1;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < cols) {
+        double s = 0.0;
+#pragma unroll
+        for (int y = 0; y < 8; ++y) s += red[y][threadIdx.x];
+        part[(int64_t)blockIdx.y * cols + c] = s;
+    }
+}
+__global__ void coldot_finish_kernel(const double* part, int64_t nchunks, int64_t cols, double* out) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    double s = 0.0;
+    for (int64_t k = 0; k < nchunks; ++k) s += part[k * cols + c];
+    out[c] = s;
+}
 // out[r] = sum_c A(r,c) B(r,c): one warp per row
 __global__ void rowdot_kernel(const double* A, int64_t lda, const double* B, int64_t ldb, int64_t rows, int64_t cols,
                               double* out) {
@@ -131,6 +166,19 @@ int zero_upper(Ctx* c, double* A, int64_t ld, int64_t n) { return sym_launch(c, 
 int coldot(Ctx* c, const double* A, int64_t lda, const double* B, int64_t ldb, int64_t rows, int64_t cols,
            double* d_out) {
     if (cols <= 0) return 0;
+    const int64_t nchunks = (rows + CD_ROWS_PER_CHUNK - 1) / CD_ROWS_PER_CHUNK;
+    if (rows >= 4 * CD_ROWS_PER_CHUNK && cols < 148 * 128 && nchunks <= 65535) {
+        // not enough columns to fill the GPU with one thread per column: split the rows as well
+        double* part = nullptr;
+        GP_CUDA(c, cudaMallocAsync((void**)&part, sizeof(double) * nchunks * cols, c->stream));
+        dim3 grid((unsigned)((cols + 31) / 32), (unsigned)nchunks), block(32, 8);
+        coldot_part_kernel<<<grid, block, 0, c->stream>>>(A, lda, B, ldb, rows, cols, part);
+        coldot_finish_kernel<<<(unsigned)((cols + 127) / 128), 128, 0, c->stream>>>(part, nchunks, cols, d_out);
+        c->launches += 2;
+        GP_CUDA(c, cudaGetLastError());
+        GP_CUDA(c, cudaFreeAsync(part, c->stream));
+        return 0;
+    }
     coldot_kernel<<<(unsigned)((cols + 127) / 128), 128, 0, c->stream>>>(A, lda, B, ldb, rows, cols, d_out);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
