@@ -732,7 +732,7 @@ def run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist):
     """C5: ONE model of N = 131072 samples factored across all ranks (block-cyclic Cholesky, NCCL panel broadcasts,
     gpr_b200/dist.py) + distributed solve. Strong scaling of a single large problem; device-timed, max over ranks."""
     from gpr_b200 import dist as gd
-    N, nb = args.large_n, 1024
+    N, nb = args.large_n, args.large_nb
     rng = np.random.default_rng(SEED + 131)
     X = rng.uniform(-1, 1, (N, C3_D))
     Y = (np.sin(3.0 * X[:, :1]) + 0.5 * np.cos(2.0 * X[:, 1:2] + X[:, 2:3]) + 0.1 * rng.standard_normal((N, 1)))
@@ -820,6 +820,7 @@ def main():
     ap.add_argument("--skip-sparse", action="store_true")
     ap.add_argument("--skip-hostio", action="store_true")
     ap.add_argument("--large-n", type=int, default=131072)
+    ap.add_argument("--large-nb", type=int, default=1024, help="block-column width of the block-cyclic Cholesky")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")
     args = ap.parse_args()
