@@ -23,6 +23,13 @@ class _DeviceView:
         self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f8", "data": (int(ptr), False), "version": 2}
 
 
+def _oracle_rows(ks, X, rows, chunk=32):
+    """k(x_r, x_j) for the sampled rows r and every training point j, evaluated on the CPU by the oracle."""
+    from oracle import gpr_oracle as orc
+    k = orc.parse_kernel(ks)
+    return np.concatenate([orc.kernel_matrix(k, X[rows[i:i + chunk]], X) for i in range(0, len(rows), chunk)], axis=0)
+
+
 def _handle(ks, X, Y, sigma):
     import gpr_b200
     h = gpr_b200.Handle(0)
@@ -45,11 +52,15 @@ def test_c3_learn_predict_properties_at_n_32768():
     assert np.isfinite(A).all()
     # linearity of the solve in the labels
     assert np.abs(A[:, 2] - (A[:, 0] + 2.0 * A[:, 1])).max() <= 1e-10 * np.abs(A).max()
-    # defining equation on sampled rows, with an independent evaluation of the kernel rows
+    # defining equation on sampled rows. The kernel rows come from the CPU ORACLE (oracle.gpr_oracle.kernel_matrix, the
+    # numpy restatement of include/Kernel.h pinned to oracle/_ref), not from the device functor that built K: a kernel
+    # value that is wrong the same way in the Gram build and in kernel_vector would otherwise cancel out.
     rows = rng.choice(N, 192, replace=False)
-    Kr = h.kernel_vector(X[rows])                                   # 192 x N, no noise term
+    Kr = _oracle_rows(C3_KERNEL, X, rows)                           # 192 x N, no noise term
     resid = Kr @ A + sigma * sigma * A[rows] - Y[rows]
     assert np.abs(resid).max() <= 1e-10 * np.abs(Y).max()
+    # and the device's own kernel rows agree with the oracle's element-wise (the Gram parity bar, 1e-13)
+    assert np.abs(h.kernel_vector(X[rows[:16]]) - Kr[:16]).max() <= 1e-13 * np.abs(Kr).max()
     # Predict at a training point: K_i alpha = y_i - s^2 alpha_i; the credible interval is real and non-negative
     mean, ci = h.predict(X[rows], want_ci=True)
     assert np.abs(mean - (Y[rows] - sigma * sigma * A[rows])).max() <= 1e-9 * np.abs(Y).max()
@@ -118,6 +129,13 @@ def test_c4_loglik_gradient_is_the_derivative_of_the_value_at_n_16384():
     TRUE = gpr_b200.capi.LOGLIK_TRUE
     v, g, _ = h.loglik(TRUE, True, True, False)
     assert np.isfinite(v).all() and np.isfinite(g).all()
+    # alpha of this iteration against oracle-evaluated kernel rows (independent of the device functor)
+    A = h.alpha()
+    rows = rng.choice(N, 128, replace=False)
+    Kr = _oracle_rows("RationalQuadraticKernel(1,1.5,2,)", X, rows)
+    assert np.abs(Kr @ A + A[rows] - Y[rows]).max() <= 1e-10 * np.abs(Y).max()
+    # value = -1/2 y^T alpha - 1/2 log det - N/2 log 2 pi with the quadratic form recomputed on the host
+    assert abs(v[0] - (-0.5 * float(Y[:, 0] @ A[:, 0]) - 0.5 * h.logdet() - 0.5 * N * np.log(2 * np.pi))) <= 1e-8 * abs(v[0])
 
     def value(p):
         h.set_kernel(ops, p)
