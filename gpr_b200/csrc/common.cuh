@@ -75,7 +75,7 @@ struct Ctx {
     int64_t opt_nbo = 0;          // outer (trailing-update) block of the two-level Cholesky; 0 = auto (512 / 1024)
     int64_t opt_chol_left = 0;    // left-looking outer loop (long-K column updates): measured slower, see potrf.cu
     int64_t opt_lookahead = 1;    // factor panel k+1 on a second stream while update k runs
-    int64_t opt_potrf_tile = 2;    // 2: blocked register/shuffle diagonal-tile kernel, 1: unblocked shared-memory kernel
+    int64_t opt_potrf_tile = 3;    // 3: DMMA block products + fused diagonal factor/inverse (potrf_tile3_kernel), 2: round-1 scalar blocked kernel, 1: unblocked
     int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu
     int64_t opt_gemm_variant = -1; // -1: auto; 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
@@ -118,6 +118,17 @@ int fail(Ctx* c, int code, const std::string& msg);
     } while (0)
 
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+#ifdef __CUDACC__
+// FP64 tensor-core atom (SASS DMMA.8x8x4): C(8x8) += A(8x4) B(4x8). Lane (grp = lane >> 2, t4 = lane & 3) holds
+// a = A[grp][t4], b = B[t4][grp], c0 = C[grp][2 t4], c1 = C[grp][2 t4 + 1]. tcgen05 has no f64 kind, so this
+// warp-level instruction is the FP64 tensor path on sm_100a.
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+#endif
 
 // kernels / drivers (each returns 0 or an error code; all async on c->stream) -----------------
 // gram.cu

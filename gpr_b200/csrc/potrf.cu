@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include <math.h>
 #include <vector>
+#include <utility>
 
 namespace gprb200 {
 
@@ -318,6 +319,277 @@ potrf_tile2_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
     }
 }
 
+// ---- potrf_tile3_kernel: the diagonal tile with every block product on the FP64 tensor pipe -----------------------
+// Round-1 launch lists: potrf_tile2_kernel costs 0.139 ms per 128 columns, N / 128 of them in a row on ONE SM, and is
+// the exposed tail of every factorisation below N ~ 16384 (profiles/r01b_ncu_summary.md). Its time is dependent-DFMA
+// latency (~40 cycles on sm_100): scalar FMA chains in the sub-panel, trailing and inv(L) products, and a 32-column
+// serial diagonal phase with CUDA's generic rsqrt and a shared-memory round trip on the critical path. Here:
+//   (1) warp 0 factors the 32 x 32 diagonal block in registers (lane = row) AND forms its inverse in the same loop
+//       (lane = column of inv(L_dd), right-looking substitution: one FMA per remaining row, all independent), so the
+//       inverse's FMAs fill the bubbles of the pivot chain. The chain per column is shuffle -> rsqrt (MUFU seed + one
+//       cubic step, 4 dependent DFMA) -> scale -> next pivot (computed locally by the lane that owns it);
+//   (2) X = A inv(L_dd)^T, (3) trailing A -= X X^T and the block-wise assembly of inv(L) (T = sum L_ik W_kj,
+//       W_ij = -W_ii T) are DMMA.8x8x4 products out of shared memory. Leading dimensions are = 4 (mod 16) doubles, so
+//       both fragment patterns (row * LD + k and k * LD + row over 4 x 4 lanes of a half-warp) hit 16 distinct 8-byte
+//       bank slots.
+// Measured (B200, tools/chol_r02.py): 0.139 -> 0.064 ms per tile; Cholesky N = 4096 5.46 -> 3.67 ms, 8192 13.4 -> 10.6,
+// 16384 56.4 -> 52.9, 32768 373.4 -> 369.3.
+constexpr int P3_THREADS = 256;
+constexpr int P3_WARPS = P3_THREADS / 32;
+constexpr int P3_IB = 32;
+constexpr int P3_LD = NB + 4;      // 132
+constexpr int P3_WLD = P3_IB + 4;  // 36
+constexpr size_t P3_SMEM =
+    sizeof(double) * ((size_t)NB * P3_LD + 4 * P3_IB * P3_WLD + 3 * P3_IB * P3_WLD + 2 * P3_IB);
+
+// 1 / sqrt(d) for a normal positive d: MUFU.RSQ64H seed (relative error ~2^-22) and one third-order step
+// y <- y + y e (1/2 + 3/8 e), e = 1 - d y^2 (error ~ e^3): four dependent DFMA instead of the generic routine.
+__device__ __forceinline__ double rsqrt_pos(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    const double t = d * y;
+    const double e = fma(-t, y, 1.0);
+    const double ye = y * e;
+    const double p = fma(0.375, e, 0.5);
+    return fma(ye, p, y);
+}
+
+// One column of the fused diagonal phase. J is a template parameter so that every index into a[] / s[] is a
+// compile-time constant: with a plain doubly unrolled loop nvcc left the long inner loops rolled and put both arrays in
+// local memory (708 LDL / 985 STL in the first build).
+template <int J>
+__device__ __forceinline__ void diag_step(double (&a)[P3_IB], double (&s)[P3_IB], double& dnext, int& fail_at, double* cb,
+                                          int lane) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const double djj = dnext;
+    // not positive (or not a normal number): leading minor c0 + J + 1 is not positive definite
+    if (fail_at < 0 && !(djj >= 2.2250738585072014e-308 && djj <= 1.7976931348623157e308)) fail_at = J;
+    const double y = rsqrt_pos(djj);
+    const double aj = (lane == J) ? djj * y : a[J] * y;   // zero above the diagonal stays zero
+    a[J] = aj;
+    if (J + 1 < P3_IB) {
+        // the next pivot needs only lane J+1's own entries: no shared-memory round trip on the chain
+        const double pv = fma(-aj, aj, a[(J + 1) % P3_IB]);
+        dnext = __shfl_sync(FULL, pv, (J + 1) % P3_IB);
+    }
+    double* cj = cb + (J & 1) * P3_IB;
+    cj[lane] = aj;
+    __syncwarp();
+    const double wj = s[J] * y;   // W(J, lane); zero for lane > J
+    s[J] = wj;
+#pragma unroll
+    for (int k = J + 1; k < P3_IB; ++k) {
+        const double ck = cj[k];                       // L(k, J), broadcast load
+        if (lane >= k) a[k] = fma(-aj, ck, a[k]);
+        s[k] = fma(-ck, wj, s[k]);
+    }
+}
+template <int... Js>
+__device__ __forceinline__ void diag_all(std::integer_sequence<int, Js...>, double (&a)[P3_IB], double (&s)[P3_IB],
+                                         double& dnext, int& fail_at, double* cb, int lane) {
+    (diag_step<Js>(a, s, dnext, fail_at, cb, lane), ...);
+}
+
+__global__ void __launch_bounds__(P3_THREADS, 1)
+potrf_tile3_kernel(double* __restrict__ A, int64_t lda, int n, double* __restrict__ invL, int* info, int col0) {
+    extern __shared__ __align__(16) double sm3[];
+    double* S = sm3;                                  // [NB][P3_LD]: lower = A then L; strict upper = inv(L)^T blocks
+    double* Wd = S + NB * P3_LD;                      // [4][32][P3_WLD]: inverses of the diagonal blocks, row-major
+    double* Tm = Wd + 4 * P3_IB * P3_WLD;             // [3][32][P3_WLD]: products in flight
+    double* cb = Tm + 3 * P3_IB * P3_WLD;             // [2][32]: column broadcast of the diagonal phase
+    __shared__ int bad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int grp = lane >> 2, t4 = lane & 3;
+    constexpr unsigned FULL = 0xffffffffu;
+    if (tid == 0) bad = 0;
+    // rows / columns >= n are padded with the identity so that every block is a full 32 x 32 problem
+    for (int e = tid; e < NB * NB; e += P3_THREADS) {
+        const int r = e >> 7, c = e & (NB - 1);
+        double v = 0.0;
+        if (r < n && c <= r) v = A[(int64_t)r * lda + c];
+        else if (r >= n && c == r) v = 1.0;
+        S[r * P3_LD + c] = v;
+    }
+    __syncthreads();
+
+    for (int b = 0; b < NB / P3_IB; ++b) {
+        const int c0 = b * P3_IB;
+        if (c0 >= n) break;
+        // ---- (1) warp 0: L_dd and inv(L_dd) in one pass
+        if (warp == 0) {
+            double a[P3_IB];   // row `lane` of the block: a[k] = A(lane, k), zero for k > lane
+            double s[P3_IB];   // column `lane` of the running right-hand side of L W = I; s[i] becomes W(i, lane)
+#pragma unroll
+            for (int k = 0; k < P3_IB; ++k) {
+                a[k] = (k <= lane) ? S[(c0 + lane) * P3_LD + c0 + k] : 0.0;
+                s[k] = (k == lane) ? 1.0 : 0.0;
+            }
+            int fail_at = -1;
+            double dnext = __shfl_sync(FULL, a[0], 0);
+            diag_all(std::make_integer_sequence<int, P3_IB>{}, a, s, dnext, fail_at, cb, lane);
+            if (fail_at >= 0) {
+                if (lane == 0) {
+                    bad = 1;
+                    atomicCAS(info, 0, col0 + c0 + fail_at + 1);
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < P3_IB; ++k)
+                    if (k <= lane) S[(c0 + lane) * P3_LD + c0 + k] = a[k];
+#pragma unroll
+                for (int i = 0; i < P3_IB; ++i) Wd[(b * P3_IB + i) * P3_WLD + lane] = s[i];
+            }
+        }
+        __syncthreads();
+        if (bad) return;  // A is left untouched; INFO tells the caller
+        const int r0 = c0 + P3_IB;  // first row / column of the trailing part
+        if (r0 >= NB) break;
+        // ---- (2) rows below: X = A[r0.., c0..c0+32) W_dd^T. A warp owns strips of 8 rows, so the in-place store is safe.
+        {
+            const double* Wb = Wd + b * P3_IB * P3_WLD;
+            const int nstrips = (NB - r0) / 8;
+            for (int st = warp; st < nstrips; st += P3_WARPS) {
+                double* row = S + (r0 + st * 8 + grp) * P3_LD + c0;
+                double af[8];
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) af[kk] = row[kk * 4 + t4];
+                double acc[4][2];
+#pragma unroll
+                for (int nn = 0; nn < 4; ++nn) {
+                    acc[nn][0] = acc[nn][1] = 0.0;
+#pragma unroll
+                    for (int kk = 0; kk < 2 * nn + 2; ++kk)   // W_dd(j, k) = 0 for k > j
+                        dmma884(acc[nn][0], acc[nn][1], af[kk], Wb[(nn * 8 + grp) * P3_WLD + kk * 4 + t4]);
+                }
+                __syncwarp();
+#pragma unroll
+                for (int nn = 0; nn < 4; ++nn)
+                    *reinterpret_cast<double2*>(row + nn * 8 + 2 * t4) = make_double2(acc[nn][0], acc[nn][1]);
+            }
+        }
+        __syncthreads();
+        // ---- (3) trailing lower triangle: A[r][c] -= sum_k X[r][k] X[c][k] in 16 x 16 warp tiles
+        {
+            const int nt = (NB - r0) / 16;
+            const int ntiles = nt * (nt + 1) / 2;
+            for (int t = warp; t < ntiles; t += P3_WARPS) {
+                int ti = 0;
+                while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+                const int tj = t - ti * (ti + 1) / 2;
+                const double* xr = S + (r0 + ti * 16 + grp) * P3_LD + c0 + t4;
+                const double* xc = S + (r0 + tj * 16 + grp) * P3_LD + c0 + t4;
+                double* cr = S + (r0 + ti * 16 + grp) * P3_LD + r0 + tj * 16 + 2 * t4;
+                double acc[2][2][2];
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const double2 v = *reinterpret_cast<const double2*>(cr + i * 8 * P3_LD + j * 8);
+                        acc[i][j][0] = v.x;
+                        acc[i][j][1] = v.y;
+                    }
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    const double a0 = -xr[kk * 4], a1 = -xr[8 * P3_LD + kk * 4];
+                    const double b0 = xc[kk * 4], b1 = xc[8 * P3_LD + kk * 4];
+                    dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+                    dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+                    dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+                    dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+                }
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+                        if (ti != tj || j <= i)   // the upper 8 x 8 atom of a diagonal tile is not part of L
+                            *reinterpret_cast<double2*>(cr + i * 8 * P3_LD + j * 8) = make_double2(acc[i][j][0], acc[i][j][1]);
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- L back to global (lower triangle incl. diagonal)
+    for (int e = tid; e < NB * NB; e += P3_THREADS) {
+        const int r = e >> 7, c = e & (NB - 1);
+        if (r < n && c <= r) A[(int64_t)r * lda + c] = S[r * P3_LD + c];
+    }
+    // ---- inv(L): diagonal blocks are Wd; block (i, j), i > j: W_ij = -W_ii (sum_{k=j}^{i-1} L_ik W_kj), stored
+    // TRANSPOSED in the strict upper part of S: W_ij(r, c) lives at S[32 j + c][32 i + r]. Both products run as
+    // 16 x 16 DMMA warp tiles (4 per 32 x 32 block).
+    constexpr int NBLK = NB / P3_IB;
+    for (int dist = 1; dist < NBLK; ++dist) {
+        const int nprod = NBLK - dist;  // blocks (i, i - dist), i = dist .. NBLK-1
+        for (int t = warp; t < nprod * 4; t += P3_WARPS) {
+            const int p = t >> 2, m0 = ((t >> 1) & 1) * 16, n0 = (t & 1) * 16;
+            const int i = dist + p, j = p;
+            double acc[2][2][2] = {};
+            for (int k = j; k < i; ++k) {
+                const double* Lik = S + (P3_IB * i + m0 + grp) * P3_LD + P3_IB * k + t4;
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    double b0, b1;
+                    if (k == j) {   // W_jj row-major in Wd: B[kr][c]
+                        const double* Wjj = Wd + (j * P3_IB + kk * 4 + t4) * P3_WLD + n0 + grp;
+                        b0 = Wjj[0];
+                        b1 = Wjj[8];
+                    } else {        // W_kj transposed in S: B[kr][c] at S[32 j + c][32 k + kr]
+                        const double* Wkj = S + (P3_IB * j + n0 + grp) * P3_LD + P3_IB * k + kk * 4 + t4;
+                        b0 = Wkj[0];
+                        b1 = Wkj[8 * P3_LD];
+                    }
+                    const double a0 = Lik[kk * 4], a1 = Lik[8 * P3_LD + kk * 4];
+                    dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+                    dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+                    dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+                    dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+                }
+            }
+            double* T = Tm + (p * P3_IB + m0 + grp) * P3_WLD + n0 + 2 * t4;
+#pragma unroll
+            for (int ii = 0; ii < 2; ++ii)
+#pragma unroll
+                for (int jj = 0; jj < 2; ++jj)
+                    *reinterpret_cast<double2*>(T + ii * 8 * P3_WLD + jj * 8) = make_double2(acc[ii][jj][0], acc[ii][jj][1]);
+        }
+        __syncthreads();
+        for (int t = warp; t < nprod * 4; t += P3_WARPS) {
+            const int p = t >> 2, m0 = ((t >> 1) & 1) * 16, n0 = (t & 1) * 16;
+            const int i = dist + p, j = p;
+            const double* Wii = Wd + (i * P3_IB + m0 + grp) * P3_WLD + t4;
+            const double* T = Tm + (p * P3_IB + t4) * P3_WLD + n0 + grp;
+            double acc[2][2][2] = {};
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                if (kk * 4 > m0 + 15) break;   // W_ii(r, t) = 0 for t > r
+                const double a0 = -Wii[kk * 4], a1 = -Wii[8 * P3_WLD + kk * 4];
+                const double b0 = T[kk * 4 * P3_WLD], b1 = T[kk * 4 * P3_WLD + 8];
+                dmma884(acc[0][0][0], acc[0][0][1], a0, b0);
+                dmma884(acc[0][1][0], acc[0][1][1], a0, b1);
+                dmma884(acc[1][0][0], acc[1][0][1], a1, b0);
+                dmma884(acc[1][1][0], acc[1][1][1], a1, b1);
+            }
+#pragma unroll
+            for (int ii = 0; ii < 2; ++ii)
+#pragma unroll
+                for (int jj = 0; jj < 2; ++jj) {
+                    double* dst = S + (P3_IB * j + n0 + jj * 8 + 2 * t4) * P3_LD + P3_IB * i + m0 + ii * 8 + grp;
+                    dst[0] = acc[ii][jj][0];
+                    dst[P3_LD] = acc[ii][jj][1];
+                }
+        }
+        __syncthreads();
+    }
+    for (int e = tid; e < NB * NB; e += P3_THREADS) {
+        const int r = e >> 7, c = e & (NB - 1);
+        double v = 0.0;
+        if (r < n && c <= r) {
+            const int bi = r / P3_IB, bj = c / P3_IB;
+            v = (bi == bj) ? Wd[(bi * P3_IB + (r - bi * P3_IB)) * P3_WLD + (c - bj * P3_IB)] : S[c * P3_LD + r];
+        }
+        invL[e] = v;
+    }
+}
+
 __global__ void logdet_kernel(const double* L, int64_t ld, int64_t n, double* out) {
     // single CTA, fixed order: deterministic
     __shared__ double red[32];
@@ -341,7 +613,9 @@ static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, in
         const int n = (int)((K0 + W - k0 < NB) ? (K0 + W - k0) : NB);
         double* Akk = A + k0 * ld + k0;
         double* invk = invL + (k0 / NB) * (int64_t)NB * NB;
-        if (c->opt_potrf_tile == 2)
+        if (c->opt_potrf_tile == 3)
+            potrf_tile3_kernel<<<1, P3_THREADS, P3_SMEM, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+        else if (c->opt_potrf_tile == 2)
             potrf_tile2_kernel<<<1, P2_THREADS, P2_SMEM, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
         else
             potrf_tile_kernel<<<1, PT_THREADS, smem, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
@@ -472,6 +746,7 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
     const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
+    GP_CUDA(c, cudaFuncSetAttribute(potrf_tile3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P3_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     int64_t NBO = c->opt_nbo;
     // measured on B200 (tools/chol_sweep2.py): 256 wins at N = 8192, 512 at 16384, 768-1024 from 24576
@@ -572,6 +847,7 @@ int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* 
     const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
+    GP_CUDA(c, cudaFuncSetAttribute(potrf_tile3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P3_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     (void)col0;
     GP_TRY(factor_panel(c, P, ld, rows, 0, w, invL, smem, c->stream));
