@@ -143,7 +143,11 @@ void RunFused() {
         Mat f = pca.GetReconstruction(w);
         for (long i = 0; i < D; ++i) e = std::max(e, std::fabs(f(i, 0) - fields(i, t)));
     }
-    EXPECT(ew <= 1e-13, "P4 fused weights == Predict");
+    std::printf("          P4: max |fused weight - Predict| = %.3e, max |field difference| = %.3e\n", ew, e);
+    // the fused call takes the batched GEMM (T = 7), Predict the one-point GEMV: two summation orders of
+    // sum_n kx_n alpha_nk over N = 60 terms with |alpha| ~ 1e2 (sigma_n = 0.1) differ by up to N eps |kx alpha| ~ 1e-12
+    // (measured 0.6e-13 with the round-1 tile kernel's rounding of L, 1.03e-13 with potrf_tile3_kernel's)
+    EXPECT(ew <= 1e-12, "P4 fused weights == Predict");
     EXPECT(e <= 1e-12, "P4 PredictReconstruction == GetReconstruction(Predict)");
     bool threw = false;
     try {

@@ -3,8 +3,8 @@ reference's own code (oracle/_ref: lib/GaussianProcess.cpp compiled unmodified; 
 
   C1  N = 1000, d = 1, x_i = 4 * 2 pi i / N, y = sin x, GaussianKernel(0.5, 1), sigma_n = 0.01, T = 1000
       (the scaled-up tests/GaussianProcessTest.cpp:35-76 of SURVEY 8(d)). cond(K + s^2 I) is ~1e6-1e7 here, orders
-      worse than the sigma_n = 1 problems elsewhere in the suite; it is computed and printed, and the alpha
-      tolerance is stated against it (two backward-stable solvers differ by ~cond * eps).
+      worse than the sigma_n = 1 problems elsewhere in the suite; it is computed and printed. alpha is held to 1e-9
+      against a long-double-refined solution; the reference's own explicit-inverse alpha is 3.9e-9 from it.
   C2  N = 4096, d = 30, GaussianKernel(1.5 sqrt(30), 1), sigma_n = 1, 32 of the 786432 output columns,
       Predict with T = 1 (the GEMV path of apps/GaussianProcessPredict.cpp:185-193) and T = 256 (batched GEMM).
   L0  GaussianLikelihood::operator() (include/Likelihood.h:106-139) against the `lik_m1` goldens.
@@ -61,15 +61,27 @@ def test_c1_exact_configuration_against_the_reference():
     mean, ci = h.predict(Xs, want_ci=True)
     one = np.stack([h.predict(x[None, :])[0] for x in Xs[::37]])
     h.close()
-    # alpha: both solvers are backward stable; their difference is bounded by ~cond * eps (stated, not 1e-9 blindly)
-    e_alpha = rel_err(a, a_ref)
-    print("C1: alpha rel err %.3e (cond * eps = %.3e)" % (e_alpha, cond * EPS))
-    assert e_alpha <= max(1e-9, 20.0 * cond * EPS)
+    # alpha. "Truth" = a double Cholesky solve of the same K refined four times with long-double residuals. Measured
+    # here and on the B200: the reference's explicit LU inverse times Y (lib/GaussianProcess.cpp:661) is 3.9e-9 from
+    # it at this conditioning (its residual K alpha - y is 4e-11), a factor-and-solve is 4e-12 from it. So the 1e-9
+    # bar is held against the truth, and the distance to the reference is bounded by the reference's OWN error.
+    import scipy.linalg as sl
+    cf = sl.cho_factor(K, lower=True)
+    at = sl.cho_solve(cf, Y).astype(np.longdouble)
+    Kl, Yl = K.astype(np.longdouble), Y.astype(np.longdouble)
+    for _ in range(4):
+        at = at + sl.cho_solve(cf, (Yl - Kl @ at).astype(np.float64)).astype(np.longdouble)
+    a_true = at.astype(np.float64)
+    e_ours, e_ref, e_alpha = rel_err(a, a_true), rel_err(a_ref, a_true), rel_err(a, a_ref)
+    print("C1: alpha vs refined truth: ours %.3e, reference %.3e; ours vs reference %.3e (cond * eps = %.3e)"
+          % (e_ours, e_ref, e_alpha, cond * EPS))
+    assert e_ours <= 1e-9
+    assert e_alpha <= max(1e-9, 2.0 * e_ref)
     # the residual of the defining equation is at rounding level for OUR alpha (does not depend on cond)
     assert np.abs(K @ a - Y).max() <= 1e-11 * max(1.0, np.abs(a).max())
     assert rel_err(mean, mean_ref) <= 1e-9
     assert rel_err(one, mean_ref[::37]) <= 1e-9
-    assert np.abs(mean[:, 0] - np.sin(Xs[:, 0])).max() <= 1e-3          # it is a sin regression
+    assert np.abs(mean[:, 0] - np.sin(Xs[:, 0])).max() <= 5e-3          # sanity only (not parity): it IS a sin regression; 1.1e-3 at the interval edge
     assert np.max(np.abs(ci - ci_ref)) <= 1e-8 * max(1.0, ci_ref.max())
 
 
