@@ -7,6 +7,8 @@
 // in flight. Rows are split across blockIdx.y so the grid is several waves of 148 SMs even when M
 // is small; partials are summed in a fixed order (deterministic).
 #include "common.cuh"
+#include <mutex>
+#include <string>
 
 namespace gprb200 {
 
@@ -119,4 +121,76 @@ int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, in
     return 0;
 }
 
+// ---- allocation-free variant of gemv_t (gprb200_gemv_t_noalloc_dev, include/gprb200.h) -------------------------------
+// The row-split partial sums live in a file-scope device array instead of a cudaMallocAsync buffer, for callers that
+// cannot allocate (CUDA graph capture, tight serving loops). GV_SCRATCH_DOUBLES doubles = 32 MiB are held by every GPU
+// that loads the library until the process exits. In HOST code the array's name is only a stand-in: the device
+// address is taken with cudaGetSymbolAddress once per device (with that device current) and passed to the kernels.
+constexpr int64_t GV_SCRATCH_DOUBLES = 4ll << 20;
+static __device__ __align__(256) double g_gemv_scratch[GV_SCRATCH_DOUBLES];
+constexpr int GV_MAX_DEVICES = 64;
+static double* g_gemv_scratch_ptr[GV_MAX_DEVICES] = {nullptr};
+static std::mutex g_gemv_scratch_mutex;
+
+// same split geometry as gemv_t above (so both entry points sum in the same order)
+static void gemv_geometry(int64_t N, int64_t M, int64_t& col_blocks, int64_t& splits, int64_t& rows_per_split) {
+    col_blocks = (M + 2 * GV_THREADS - 1) / (2 * GV_THREADS);
+    splits = (148 * 8 * 8 + col_blocks - 1) / col_blocks;
+    const int64_t max_splits = (N + 255) / 256;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    if (splits > 65535) splits = 65535;
+    rows_per_split = (N + splits - 1) / splits;
+    if (rows_per_split > 4096) rows_per_split = 4096;
+    splits = (N + rows_per_split - 1) / rows_per_split;
+}
+
+static int gemv_t_noalloc(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out) {
+    if (c->device < 0 || c->device >= GV_MAX_DEVICES) return fail(c, -2, "gemv_t_noalloc: device index out of range");
+    GP_CUDA(c, cudaSetDevice(c->device));
+    int64_t col_blocks, splits, rows_per_split;
+    gemv_geometry(N, M, col_blocks, splits, rows_per_split);
+    const int64_t ldp = round_up(M, 2);
+    if (splits > 65535 || col_blocks > 0x7fffffff)
+        return fail(c, -2, "gemv_t_noalloc: N / M exceed the launch grid");
+    if (splits > 1 && splits * ldp > GV_SCRATCH_DOUBLES)
+        return fail(c, -2, "gemv_t_noalloc: " + std::to_string(splits) + " row splits x " + std::to_string(ldp) +
+                               " columns = " + std::to_string(splits * ldp) + " partial sums exceed the static scratch of " +
+                               std::to_string(GV_SCRATCH_DOUBLES) + " doubles (32 MiB); use gprb200_predict_dev");
+    double* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_gemv_scratch_mutex);
+        if (!g_gemv_scratch_ptr[c->device]) {   // set-up, once per device, this device current
+            double* p = nullptr;
+            GP_CUDA(c, cudaGetSymbolAddress((void**)&p, g_gemv_scratch));
+            g_gemv_scratch_ptr[c->device] = p;
+        }
+        scratch = g_gemv_scratch_ptr[c->device];
+    }
+    // nothing in the scratch has to start at zero: every partial the reduction reads is written by this call's
+    // gemv_t_kernel first (row splits x columns < M); the contents of the previous call are simply overwritten
+    double* partial = (splits == 1) ? out : scratch;
+    gemv_t_kernel<<<dim3((unsigned)col_blocks, (unsigned)splits), GV_THREADS, sizeof(double) * rows_per_split,
+                    c->stream>>>(kx, A, lda, N, M, rows_per_split, partial, splits == 1 ? 0 : ldp);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    if (splits > 1) {
+        gemv_reduce_kernel<<<(unsigned)((M + 255) / 256), 256, 0, c->stream>>>(partial, ldp, (int)splits, M, out);
+        ++c->launches;
+        GP_CUDA(c, cudaGetLastError());
+    }
+    return 0;
+}
+
 }  // namespace gprb200
+
+extern "C" int gprb200_gemv_t_noalloc_dev(gprb200_handle h, const double* dKx, const double* dA, int64_t lda, int64_t N,
+                                          int64_t M, double* dOut) {
+    if (!h) return -2;
+    gprb200::Ctx* c = h;
+    if (!dKx || !dA || !dOut || N <= 0 || M <= 0 || lda < M)
+        return gprb200::fail(c, -2, "gemv_t_noalloc: need device pointers, N > 0, M > 0 and lda >= M");
+    if ((lda & 1) || (reinterpret_cast<uintptr_t>(dA) & 15))
+        return gprb200::fail(c, -2, "gemv_t_noalloc: A must be 16-byte aligned with an even leading dimension");
+    return gprb200::gemv_t_noalloc(c, dKx, dA, lda, N, M, dOut);
+}

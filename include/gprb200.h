@@ -186,6 +186,20 @@ int gprb200_predict_derivative(gprb200_handle h, const double* x, double* mean, 
 /* ComputeKernelVector (lib/GaussianProcess.cpp:675-693) for T points: Kx is T x N */
 int gprb200_kernel_vector(gprb200_handle h, const double* Xs, int64_t T, double* Kx);
 
+/* Allocation-free Predict GEMV. NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * dOut[m] = sum_n dKx[n] dA[n * lda + m] (N x M row-major dA, e.g. the regression vectors from gprb200_get_alpha_dev
+ * with dKx the kernel vector of one test point): the product gprb200_predict_dev forms for T = 1, same kernels, same
+ * summation order. All pointers are DEVICE pointers; dA 16-byte aligned, lda even and >= M. The row-split partial
+ * sums go to a file-scope static __device__ array of 4 Mi doubles (32 MiB per GPU, held until the process exits)
+ * instead of a stream-ordered allocation; the call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limit: splits * round_up(M, 2) <= 4194304, splits = ceil(N / rows_per_split) as chosen by the kernel's geometry
+ * (e.g. N = 4096: up to M = 262144 columns); larger shapes return -2 with a message naming the limit.
+ * Every call on a GPU shares that one array (it keeps the last call's contents; nothing needs to start at zero):
+ * calls that OVERLAP on the same GPU - different streams or handles - race. Serialise them. */
+int gprb200_gemv_t_noalloc_dev(gprb200_handle h, const double* dKx, const double* dA, int64_t lda, int64_t N, int64_t M,
+                               double* dOut);
+
 /* ---- Likelihood -------------------------------------------------------------------------- */
 /* ComputeDerivativeKernelMatrix (lib/GaussianProcess.cpp:460-495): D is (P*N) x N, block p at rows [pN,(p+1)N). */
 int gprb200_dgram(gprb200_handle h, double* D_out);
