@@ -369,6 +369,9 @@ int gprb200_create(gprb200_handle* h, int device) {
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
         if (cudaStreamCreateWithPriority(&c->panel_stream, cudaStreamNonBlocking, hi) != cudaSuccess)
             c->panel_stream = nullptr;  // look-ahead is then disabled
+        if (cudaStreamCreateWithPriority(&c->aux_stream, cudaStreamNonBlocking, hi) != cudaSuccess) c->aux_stream = nullptr;
+        if (cudaEventCreateWithFlags(&c->ev_pcrit, cudaEventDisableTiming) != cudaSuccess) c->ev_pcrit = nullptr;
+        if (cudaEventCreateWithFlags(&c->ev_paux, cudaEventDisableTiming) != cudaSuccess) c->ev_paux = nullptr;
     }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -396,6 +399,9 @@ int gprb200_destroy(gprb200_handle h) {
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     if (c->panel_stream) cudaStreamDestroy(c->panel_stream);
+    if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+    if (c->ev_pcrit) cudaEventDestroy(c->ev_pcrit);
+    if (c->ev_paux) cudaEventDestroy(c->ev_paux);
     delete c;
     return 0;
 }
@@ -451,7 +457,7 @@ int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
         {"gram_lower_only", &h->opt_gram_lower_only}, {"gram_terms", &h->opt_gram_terms}, {"stream_io", &h->opt_stream_io}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead}, {"chol_left", &h->opt_chol_left},
-        {"gemm_stages", &h->opt_gemm_stages}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
+        {"gemm_stages", &h->opt_gemm_stages}, {"panel_split", &h->opt_panel_split}, {"gemm_small", &h->opt_gemm_small}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
         {"profile", &h->opt_profile}};
     if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
     for (auto& o : opts)

@@ -343,6 +343,11 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     const int variant = c->opt_gemm_variant >= 0 ? (int)c->opt_gemm_variant : ((g.beta != 0.0 && g.K <= 2048) ? 1 : 0);
     // variant 1: 64x16 warp tiles, 8 warps per CTA, 16 warps per SM (<= 128 registers): four warps per scheduler
     // keep the DMMA pipe fed while another CTA sits in its epilogue or at a barrier.
+    // short-K products with one column tile (the K = 128 panel solves and next-block-column updates of potrf.cu):
+    // a 128 x 128 x 128 product is 17 us of DMMA on ONE SM, and a tall panel has only m / 128 such CTAs; 32-row tiles
+    // give four times the CTAs at a quarter of the latency each
+    if (wide && form == GEMM_NT && g.K <= 256 && c->opt_gemm_small && g.batch <= 1 && g.ktri == 0)
+        return launch<32, 128, 16, 32, true, true, 3, 2>(c, g, stream);
     switch (form) {
         case GEMM_NT:
             if (wide) return launch<128, 128, 64, 32, true, true, 3, 1>(c, g, stream);

@@ -403,12 +403,31 @@ potrf_tile3_kernel(double* __restrict__ A, int64_t lda, int n, double* __restric
     constexpr unsigned FULL = 0xffffffffu;
     if (tid == 0) bad = 0;
     // rows / columns >= n are padded with the identity so that every block is a full 32 x 32 problem
-    for (int e = tid; e < NB * NB; e += P3_THREADS) {
-        const int r = e >> 7, c = e & (NB - 1);
-        double v = 0.0;
-        if (r < n && c <= r) v = A[(int64_t)r * lda + c];
-        else if (r >= n && c == r) v = 1.0;
-        S[r * P3_LD + c] = v;
+    if (n == NB && (lda & 1) == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0) {
+        // full tile: 32 independent 16-byte loads per thread, all issued before the first use (the scalar loop below
+        // cost ~12 us of exposed global latency per tile in the ncu source view, 64 dependent round trips per thread)
+        double2 v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const int e = (i * P3_THREADS + tid) * 2;
+            const int r = e >> 7, c = e & (NB - 1);
+            v[i] = (c <= r) ? *reinterpret_cast<const double2*>(A + (int64_t)r * lda + c) : make_double2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const int e = (i * P3_THREADS + tid) * 2;
+            const int r = e >> 7, c = e & (NB - 1);
+            if (c == r) v[i].y = 0.0;   // (r, r + 1) lies above the diagonal
+            *reinterpret_cast<double2*>(S + r * P3_LD + c) = v[i];
+        }
+    } else {
+        for (int e = tid; e < NB * NB; e += P3_THREADS) {
+            const int r = e >> 7, c = e & (NB - 1);
+            double v = 0.0;
+            if (r < n && c <= r) v = A[(int64_t)r * lda + c];
+            else if (r >= n && c == r) v = 1.0;
+            S[r * P3_LD + c] = v;
+        }
     }
     __syncthreads();
 
@@ -607,8 +626,17 @@ __global__ void logdet_kernel(const double* L, int64_t ld, int64_t n, double* ou
 }
 
 // One panel: columns [K0, K0 + W) of rows [K0, N), right-looking with NB-wide steps, on `st`.
+// Per 128-column step the chain  tile -> panel solve -> update  used to run back to back on `st` (round-2 launch list at
+// N = 4096: 64 + 24 + 40 us). Only the NEXT block column has to be up to date before the next tile can start, so the
+// update is split (option "panel_split"):
+//   st  : tile(k) | solve(k) | update of block column k+1 with column k | tile(k+1) | ...
+//   aux :                       wait | update of block columns k+2.. with column k      | ...
+// The two updates of one block column (by column k on aux, by column k+1 on st) read-modify-write the same memory, so
+// st waits for aux's step k before it touches block column k+2; aux is one in-order stream, which orders the rest.
 static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, int64_t W, double* invL, size_t smem,
                         cudaStream_t st) {
+    cudaStream_t aux = (c->opt_panel_split && c->aux_stream && c->ev_pcrit && c->ev_paux) ? c->aux_stream : nullptr;
+    bool aux_busy = false;
     for (int64_t k0 = K0; k0 < K0 + W; k0 += NB) {
         const int n = (int)((K0 + W - k0 < NB) ? (K0 + W - k0) : NB);
         double* Akk = A + k0 * ld + k0;
@@ -629,13 +657,32 @@ static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, in
         ps.M = (int)m; ps.N = n; ps.K = n; ps.alpha = 1.0; ps.beta = 0.0;
         GP_TRY(gemm(c, GEMM_NT, ps, st));
         const int64_t wrem = K0 + W - (k0 + n);  // panel columns still to be updated
-        if (wrem > 0) {
-            GemmArgs pu{};
-            pu.A = below; pu.lda = ld; pu.B = below; pu.ldb = ld; pu.C = A + (k0 + n) * ld + (k0 + n); pu.ldc = ld;
-            pu.M = (int)m; pu.N = (int)wrem; pu.K = n; pu.alpha = -1.0; pu.beta = 1.0;
+        if (wrem <= 0) continue;
+        GemmArgs pu{};
+        pu.A = below; pu.lda = ld; pu.B = below; pu.ldb = ld; pu.C = A + (k0 + n) * ld + (k0 + n); pu.ldc = ld;
+        pu.M = (int)m; pu.N = (int)wrem; pu.K = n; pu.alpha = -1.0; pu.beta = 1.0;
+        const int64_t nxt = (wrem < NB) ? wrem : NB;
+        if (!aux || wrem <= nxt || m <= nxt) {
+            if (aux_busy) GP_CUDA(c, cudaStreamWaitEvent(st, c->ev_paux, 0));
             GP_TRY(gemm(c, GEMM_NT, pu, st));
+            continue;
         }
+        // critical: the next block column (all rows below); it last received aux's update of the previous step
+        if (aux_busy) GP_CUDA(c, cudaStreamWaitEvent(st, c->ev_paux, 0));
+        pu.N = (int)nxt;
+        GP_TRY(gemm(c, GEMM_NT, pu, st));
+        GP_CUDA(c, cudaEventRecord(c->ev_pcrit, st));
+        GP_CUDA(c, cudaStreamWaitEvent(aux, c->ev_pcrit, 0));
+        // the rest of the panel, rows from the block after next (what lies above is not part of L)
+        GemmArgs pr{};
+        pr.A = below + nxt * ld; pr.lda = ld; pr.B = below + nxt * ld; pr.ldb = ld;
+        pr.C = A + (k0 + n + nxt) * ld + (k0 + n + nxt); pr.ldc = ld;
+        pr.M = (int)(m - nxt); pr.N = (int)(wrem - nxt); pr.K = n; pr.alpha = -1.0; pr.beta = 1.0;
+        GP_TRY(gemm(c, GEMM_NT, pr, aux));
+        GP_CUDA(c, cudaEventRecord(c->ev_paux, aux));
+        aux_busy = true;
     }
+    if (aux_busy) GP_CUDA(c, cudaStreamWaitEvent(st, c->ev_paux, 0));  // the panel is complete on `st`
     return 0;
 }
 
