@@ -41,6 +41,7 @@ _PROTOS = {
     "gprb200_get_factor": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_logdet": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "gprb200_spd_inverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_double)]),
+    "gprb200_lu_inverse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_gemm_dev": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_void_p, C.c_int64,
                                    C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_int64, C.c_int]),
     "gprb200_gram_block_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64]),
@@ -278,6 +279,14 @@ class Handle:
         v = C.c_double()
         self._ck(self.lib.gprb200_spd_inverse(self.h, _ptr(A), n, _ptr(out), C.byref(v)))
         return out, v.value
+
+    def lu_inverse(self, A):
+        """lapack::lu_invert for a general square host matrix."""
+        A = _f64(A)
+        n = A.shape[0]
+        out = np.empty((n, n))
+        self._ck(self.lib.gprb200_lu_inverse(self.h, _ptr(A), n, _ptr(out)))
+        return out
 
     def logdet(self):
         v = C.c_double()

@@ -148,6 +148,12 @@ int gprb200_get_logdet(gprb200_handle h, double* logdet);
  * = log det A. Does not touch the model held by the handle. Returns k > 0 if the leading minor k is not SPD. */
 int gprb200_spd_inverse(gprb200_handle h, const double* A, int64_t n, double* Ainv, double* logdet);
 
+/* lapack::lu_invert (include/LAPACKUtils.h:38-56, :85-97: dgetrf + dgetri) for a GENERAL square host matrix A (n x n):
+ * Ainv = inv(A) by in-place Gauss-Jordan elimination with partial pivoting on the device (the pivot choice of dgetrf).
+ * A utility of the public LAPACKUtils interface, not on the GP path (which always factors by Cholesky). n <= 32768.
+ * Returns k > 0 (dgetrf's INFO) if the matrix is exactly singular at step k or holds non-finite values. */
+int gprb200_lu_inverse(gprb200_handle h, const double* A, int64_t n, double* Ainv);
+
 /* ---- device-pointer building blocks (multi-GPU drivers, probes) -------------------------------------- */
 /* C = alpha op(A) op(B) + beta C on the FP64 tensor path, row-major, device pointers, 16-byte aligned, even lds.
  * form 0 (NT): A is M x K, B is N x K, C = A B^T; 1 (NN): B is K x N; 2 (TN): A is K x M, B is K x N, C = A^T B.
