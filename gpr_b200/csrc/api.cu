@@ -824,6 +824,16 @@ int gprb200_potrf_panel_dev(gprb200_handle h, double* dP, int64_t ld, int64_t ro
     return 0;
 }
 
+int gprb200_potrf_panel_async_dev(gprb200_handle h, double* dP, int64_t ld, int64_t rows, int64_t w, double* dInvL,
+                                  int64_t col0, int* dInfo) {
+    if (!h || !dP || !dInvL || !dInfo) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, rows >= w && w > 0 && (ld & 1) == 0 && col0 >= 0 && col0 < (1ll << 31) - w,
+                   "potrf_panel_async: need rows >= w > 0, an even leading dimension and 0 <= col0 < 2^31"));
+    return potrf_panel_async(c, dP, ld, rows, w, dInvL, (int)col0, dInfo);
+}
+
 int gprb200_trsm_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, double* dB,
                      int64_t ldb, int64_t M, int transposed) {
     if (!h || !dL || !dInvL || !dB) return -2;

@@ -153,6 +153,7 @@ int gemm_skinny(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream); 
 // potrf.cu
 int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host);
 int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* info_host);
+int potrf_panel_async(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* dinfo);
 int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host);
 // solve.cu
 int trsm_lower_fwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,

@@ -634,7 +634,8 @@ __global__ void logdet_kernel(const double* L, int64_t ld, int64_t n, double* ou
 // The two updates of one block column (by column k on aux, by column k+1 on st) read-modify-write the same memory, so
 // st waits for aux's step k before it touches block column k+2; aux is one in-order stream, which orders the rest.
 static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, int64_t W, double* invL, size_t smem,
-                        cudaStream_t st) {
+                        cudaStream_t st, int* dinfo = nullptr, int info_base = 0) {
+    if (!dinfo) dinfo = c->dInfo;
     cudaStream_t aux = (c->opt_panel_split && c->aux_stream && c->ev_pcrit && c->ev_paux) ? c->aux_stream : nullptr;
     bool aux_busy = false;
     for (int64_t k0 = K0; k0 < K0 + W; k0 += NB) {
@@ -642,11 +643,11 @@ static int factor_panel(Ctx* c, double* A, int64_t ld, int64_t N, int64_t K0, in
         double* Akk = A + k0 * ld + k0;
         double* invk = invL + (k0 / NB) * (int64_t)NB * NB;
         if (c->opt_potrf_tile == 3)
-            potrf_tile3_kernel<<<1, P3_THREADS, P3_SMEM, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+            potrf_tile3_kernel<<<1, P3_THREADS, P3_SMEM, st>>>(Akk, ld, n, invk, dinfo, info_base + (int)k0);
         else if (c->opt_potrf_tile == 2)
-            potrf_tile2_kernel<<<1, P2_THREADS, P2_SMEM, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+            potrf_tile2_kernel<<<1, P2_THREADS, P2_SMEM, st>>>(Akk, ld, n, invk, dinfo, info_base + (int)k0);
         else
-            potrf_tile_kernel<<<1, PT_THREADS, smem, st>>>(Akk, ld, n, invk, c->dInfo, (int)k0);
+            potrf_tile_kernel<<<1, PT_THREADS, smem, st>>>(Akk, ld, n, invk, dinfo, info_base + (int)k0);
         ++c->launches;
         GP_CUDA(c, cudaGetLastError());
         const int64_t m = N - k0 - n;
@@ -903,6 +904,21 @@ int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* 
         GP_CUDA(c, cudaStreamSynchronize(c->stream));
     }
     return 0;
+}
+
+// The same without any host synchronisation: INFO stays on the device. dinfo is a caller-owned device int that is NOT
+// reset here; the first failing leading minor (col0 + local index, 1-based) wins (atomicCAS from 0), so one int can
+// collect the status of a whole multi-step, multi-GPU factorisation and be read once at the end.
+int potrf_panel_async(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* dinfo) {
+    const size_t smem = sizeof(double) * (NB * PT_LD + 2 * NB);
+    static bool attr_set[64] = {false};
+    if (c->device >= 0 && c->device < 64 && !attr_set[c->device]) {
+        GP_CUDA(c, cudaFuncSetAttribute(potrf_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        GP_CUDA(c, cudaFuncSetAttribute(potrf_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P2_SMEM));
+        GP_CUDA(c, cudaFuncSetAttribute(potrf_tile3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P3_SMEM));
+        attr_set[c->device] = true;
+    }
+    return factor_panel(c, P, ld, rows, 0, w, invL, smem, c->stream, dinfo, col0);
 }
 
 int logdet_from_factor(Ctx* c, const double* L, int64_t ld, int64_t N, double* out_host) {

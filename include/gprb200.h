@@ -171,6 +171,12 @@ int gprb200_gram_block_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_
  * rows below are solved against it (the dpotrf + dtrsm a blocked LAPACK dpotrf does per panel;
  * include/LAPACKUtils.h:59-73). dInvL: ceil(w/128) blocks of 128 x 128 (inverted diagonal blocks, for trsm_dev). */
 int gprb200_potrf_panel_dev(gprb200_handle h, double* dP, int64_t ld, int64_t rows, int64_t w, double* dInvL, int* info);
+/* The same with NO host synchronisation (multi-GPU schedules must not block the host once per panel): dInfo is a
+ * caller-owned DEVICE int that is not reset by the call; the first leading minor that is not positive definite stores
+ * col0 + its 1-based local index there (compare-and-swap from 0), so one int collects the INFO of a whole distributed
+ * factorisation and is read once at the end. */
+int gprb200_potrf_panel_async_dev(gprb200_handle h, double* dP, int64_t ld, int64_t rows, int64_t w, double* dInvL,
+                                  int64_t col0, int* dInfo);
 /* B <- L^-1 B (transposed = 0) or L^-T B (transposed != 0); L n x n lower (ldl), B n x M (ldb), dInvL as above. */
 int gprb200_trsm_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, double* dB,
                      int64_t ldb, int64_t M, int transposed);
