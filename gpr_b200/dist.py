@@ -3,25 +3,33 @@ NVLink 5 / NVSwitch) for the plumbing, every numerical step through the C-ABI of
 
 The reference (agiger/GPR) is a single-process CPU library with no distributed code at all
 (/root/reference: grep for mpi|nccl finds nothing), so everything here is new; what it must reproduce is the result of
-GaussianProcess::ComputeRegressionVectors (reference lib/GaussianProcess.cpp:642-672) and Predict (:55-61).
+GaussianProcess::ComputeRegressionVectors (reference lib/GaussianProcess.cpp:642-672), Predict (:55-61),
+GetCredibleInterval (:103-114) and GaussianLogLikelihood::GetValueAndParameterDerivatives (include/Likelihood.h:231-285).
 
-Two partitionings:
+Partitionings:
 
 * ``ShardedOutputsGP`` - the many-output model (BASELINE config C2, M = 786432 columns): the output columns of
   Y / alpha and the predicted field are independent, so each rank factors the (small) kernel matrix itself and owns
-  M / g columns. No data-path collective; an optional all_gather assembles a full prediction.
-* ``BlockCyclicGP`` - N beyond one GPU's sweet spot (config C5, N = 131072, K = 137 GB): block-cyclic Cholesky over
-  a 1 x g process grid (block column j of width nb lives on rank j mod g, lower triangle only), right-looking with
-  a one-panel look-ahead: the owner factors block column k, broadcasts it (NCCL), every rank updates the block
-  columns it owns with one tensor-core GEMM each. On NVSwitch every peer is equidistant, so the 1 x g grid's
-  larger broadcast volume (4 N^2 bytes per GPU in total, 68.7 GB at N = 131072, ~0.2 s at measured NCCL rates
-  against ~3.4 s of FP64 work per GPU at g = 8) is cheaper than a Pr x Pc grid's second, transposed broadcast and
-  distributed panel solve; the panel factorisation and its broadcast run on a side stream under the trailing update.
+  M / g columns; test points for the credible interval are split T / g with L replicated. No data-path collective;
+  optional all_gathers assemble a full prediction.
+* ``BlockCyclicGP`` - N beyond one GPU's sweet spot (config C5, N = 131072, K = 137 GB): 2-D block-cyclic Cholesky
+  over a Pr x Pc process grid, lower triangle only: block (i, j), i >= j, of nb x nb lives on rank
+  (i mod Pr) * Pc + (j mod Pc). Right-looking with a one-panel look-ahead; per step k
+      diagonal owner : L_kk = chol(A_kk) on the device, W = inv(L_kk)                      (single GPU, critical path)
+      grid column k  : W broadcast down the column (Pr ranks), every rank solves ITS rows: X_i = A_ik W^T
+      grid rows      : every rank of the column broadcasts its X rows along its grid row (Pc ranks)
+      grid columns   : the blocks that are a column operand L_jk travel down each grid column (Pr roots)
+      everyone       : A_ij -= X_i L_jk^T for the owned blocks, one tensor-core GEMM per owned block column.
+  1 x g is the degenerate case (no column communicator, the layout of round 1). INFO stays on the device for the whole
+  factorisation and is reduced once at the end: the host never waits inside the loop.
+* ``ShardedLikelihood`` - the likelihood gradient 1/2 tr((alpha alpha^T - C) dK_p) with row blocks of A = alpha alpha^T - C
+  and the matching dK rows per rank, partial sums all-reduced (P doubles).
 
 Host logic (ownership, schedule, collectives) is independent of the device: ``ops`` is the object that executes
 local block operations. ``DeviceOps`` (default) calls the CUDA library; the CPU tests in tests/test_dist_gloo.py
-inject a numpy stand-in to run the same schedule under gloo with world_size 2.
+inject a numpy stand-in to run the same schedule under gloo with world_size 2, 3 and 4 (2 x 2).
 """
+import bisect
 import ctypes
 
 import numpy as np
@@ -45,6 +53,19 @@ def column_shard(M, rank, world):
     return begin, begin + base + (1 if rank < extra else 0)
 
 
+def default_grid(world):
+    """Pr x Pc with Pr <= Pc, Pr the largest power of two with Pr^2 <= world that divides it (8 -> 2 x 4, 4 -> 2 x 2)."""
+    pr = 1
+    while (2 * pr) * (2 * pr) <= world and world % (2 * pr) == 0:
+        pr *= 2
+    return pr, world // pr
+
+
+def block_owner(i, j, Pr, Pc):
+    """Rank that owns block (i, j) of the Pr x Pc block-cyclic layout."""
+    return (i % Pr) * Pc + (j % Pc)
+
+
 class DeviceOps:
     """Local block operations on CUDA tensors through libgprb200.so. Two C-ABI handles: one bound to the main
     stream (model state: kernel + samples, trailing updates), one to the panel stream (panel factorisation)."""
@@ -60,12 +81,18 @@ class DeviceOps:
         self.hp = Handle(device_index)
         self.hp.set_stream(self.panel_stream.cuda_stream)
         self.h.set_kernel(ops, params)
-        Xd = torch.as_tensor(np.ascontiguousarray(X, dtype=np.float64)).to(self.device)
-        self.h._ck(self.h.lib.gprb200_set_train_dev(self.h.h, Xd.data_ptr(), Xd.shape[0], Xd.shape[1], None, 0,
-                                                     ctypes.c_double(sigma)))
-        self.h.N, self.h.d, self.h.M = Xd.shape[0], Xd.shape[1], 0
-        self.h.synchronize()
         self._events = {}
+        self.set_samples(X, sigma)
+
+    def set_samples(self, X, sigma):
+        """(Re)install the training inputs: N x d host array (the H2D copy of the end-to-end path) or device tensor."""
+        Xd = X if isinstance(X, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(X, dtype=np.float64))
+        with torch.cuda.stream(self.main_stream):
+            Xd = Xd.to(self.device, non_blocking=True).contiguous()
+            self.h._ck(self.h.lib.gprb200_set_train_dev(self.h.h, Xd.data_ptr(), Xd.shape[0], Xd.shape[1], None, 0,
+                                                         ctypes.c_double(sigma)))
+        self.h.N, self.h.d, self.h.M = Xd.shape[0], Xd.shape[1], 0
+        self._X = Xd
 
     # -- memory ---------------------------------------------------------------------------------------------------
     def empty(self, rows, cols):
@@ -74,8 +101,19 @@ class DeviceOps:
     def zeros(self, rows, cols):
         return torch.zeros((rows, cols), dtype=torch.float64, device=self.device)
 
+    def eye(self, n):
+        return torch.eye(n, dtype=torch.float64, device=self.device)
+
     def from_host(self, a):
-        return torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).to(self.device)
+        if isinstance(a, torch.Tensor):
+            return a.to(self.device, non_blocking=True)
+        return torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64)).to(self.device, non_blocking=True)
+
+    def new_info(self):
+        return torch.zeros(1, dtype=torch.int32, device=self.device)
+
+    def read_info(self, info):
+        return int(info.item())
 
     # -- streams / events ---------------------------------------------------------------------------------------------
     def on(self, which):
@@ -102,12 +140,12 @@ class DeviceOps:
         h = self.h
         h._ck(h.lib.gprb200_gram_block_dev(h.h, row0, out.shape[0], col0, out.shape[1], out.data_ptr(), out.stride(0)))
 
-    def potrf_panel(self, P, invL, which="panel"):
+    def potrf_block(self, P, invL, col0, info, which="panel"):
+        """Cholesky of the top w x w block of P (rows x w) and the rows below solved against it, no host sync: the
+        first failing leading minor (col0 + index, 1-based) is left in the device int `info`."""
         h = self._handle(which)
-        info = ctypes.c_int(0)
-        h._ck(h.lib.gprb200_potrf_panel_dev(h.h, P.data_ptr(), P.stride(0), P.shape[0], P.shape[1], invL.data_ptr(),
-                                            ctypes.byref(info)))
-        return info.value
+        h._ck(h.lib.gprb200_potrf_panel_async_dev(h.h, P.data_ptr(), P.stride(0), P.shape[0], P.shape[1], invL.data_ptr(),
+                                                  int(col0), info.data_ptr()))
 
     def gemm(self, form, A, B, Cm, alpha, beta, which="main"):
         """form 'NT': C = alpha A B^T + beta C; 'NN': A B; 'TN': A^T B."""
@@ -144,14 +182,14 @@ class DeviceOps:
 
 
 class BlockCyclicGP:
-    """GP Learn for N beyond one GPU: block-cyclic Cholesky of K + sigma^2 I over the ranks of `group`, then
-    alpha = (K + sigma^2 I)^-1 Y by distributed forward / backward substitution (Y has few columns here; the
-    many-column case is ShardedOutputsGP). Every rank ends with the full alpha and log det.
+    """GP Learn for N beyond one GPU: 2-D block-cyclic Cholesky of K + sigma^2 I over the ranks of `group` (Pr x Pc
+    grid, default 1 x world), then alpha = (K + sigma^2 I)^-1 Y by distributed forward / backward substitution (Y has
+    few columns here; the many-column case is ShardedOutputsGP). Every rank ends with the full alpha and log det.
 
     Replaces, for large N, the reference's single-process InvertKernelMatrix + C * Y
     (lib/GaussianProcess.cpp:531-560, :661)."""
 
-    def __init__(self, ops, N, nb=1024, group=None):
+    def __init__(self, ops, N, nb=1024, grid=None, group=None):
         self.ops = ops
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -160,103 +198,232 @@ class BlockCyclicGP:
         self.nb = int(nb)
         if self.nb % 128 != 0:
             raise ValueError("BlockCyclicGP: nb must be a multiple of 128 (the Cholesky diagonal block)")
+        self.Pr, self.Pc = (1, self.world) if grid is None else (int(grid[0]), int(grid[1]))
+        if self.Pr * self.Pc != self.world:
+            raise ValueError("BlockCyclicGP: grid %d x %d does not match world size %d" % (self.Pr, self.Pc, self.world))
+        self.pr, self.pc = divmod(self.rank, self.Pc)
         self.nblk = (self.N + self.nb - 1) // self.nb
-        self.mine = owned_blocks(self.nblk, self.rank, self.world)
-        self.cols = {}      # j -> (N - j nb) x w_j tensor: block column j of K, later of L, rows j nb .. N
-        self.invl = {}      # j -> inverted 128 x 128 diagonal blocks of L_jj
+        self.hgt = [min(self.nb, self.N - i * self.nb) for i in range(self.nblk)]   # block heights = widths
+        self.myrows = [i for i in range(self.nblk) if i % self.Pr == self.pr]       # block rows stacked in every local panel
+        self.roff = {}
+        o = 0
+        for i in self.myrows:
+            self.roff[i] = o
+            o += self.hgt[i]
+        self.H = o
+        self.mine = [j for j in range(self.nblk) if j % self.Pc == self.pc]         # owned block columns
+        self._ranks = list(range(self.world))
+        if group is not None and self.world > 1:
+            self._ranks = dist.get_process_group_ranks(group)
+        self.row_group, self.col_group = self._make_groups()
+        self.cols = {}      # j -> stacked blocks (i, j), i in myrows, i >= j: (H - off(j)) x even(w_j); K, later L
+        self.invl = {}      # j -> inverted 128 x 128 diagonal blocks of L_jj (diagonal owner only)
         self.factored = False
         self.logdet = None
-        self.stats = {"bcast_bytes": 0, "gemm_flops": 0.0}
+        self.info = None
+        self._bufs = None
+        self.stats = {"bcast_bytes": 0, "gemm_flops": 0.0, "collectives": 0}
 
-    # -- helpers ---------------------------------------------------------------------------------------------------
-    def _width(self, j):
-        return min(self.nb, self.N - j * self.nb)
+    # -- grid helpers -----------------------------------------------------------------------------------------------
+    def _grank(self, r, c):
+        return self._ranks[r * self.Pc + c]
 
-    def _bcast(self, t, src):
-        if self.world > 1:
-            dist.broadcast(t, src=dist.get_global_rank(self.group, src) if self.group is not None else src,
-                           group=self.group)
+    def _make_groups(self):
+        """Row communicators (Pc ranks, same grid row) and column communicators (Pr ranks, same grid column). Every
+        rank creates every group, in the same order (torch.distributed.new_group is collective)."""
+        if self.world == 1:
+            return None, None
+        row = col = None
+        if self.Pc > 1:
+            if self.Pr == 1:
+                row = self.group if self.group is not None else dist.group.WORLD
+            else:
+                for r in range(self.Pr):
+                    g = dist.new_group([self._grank(r, c) for c in range(self.Pc)])
+                    if r == self.pr:
+                        row = g
+        if self.Pr > 1:
+            if self.Pc == 1:
+                col = self.group if self.group is not None else dist.group.WORLD
+            else:
+                for c in range(self.Pc):
+                    g = dist.new_group([self._grank(r, c) for r in range(self.Pr)])
+                    if c == self.pc:
+                        col = g
+        return row, col
+
+    def _first_row_at_or_after(self, j):
+        """Offset (in rows of a stacked panel) of the first owned block row i >= j, and that i (or None)."""
+        s = bisect.bisect_left(self.myrows, j)
+        if s == len(self.myrows):
+            return self.H, None
+        i = self.myrows[s]
+        return self.roff[i], i
+
+    def _bcast(self, t, src, group):
+        dist.broadcast(t, src=src, group=group)
         self.stats["bcast_bytes"] += t.numel() * 8
+        self.stats["collectives"] += 1
 
-    # -- Gram: every rank builds exactly the block columns it owns (no exchange) ------------------------------------
-    def build_gram(self):
+    # -- Gram: every rank builds exactly the blocks it owns (no exchange) -------------------------------------------
+    def _alloc(self):
         ops = self.ops
         with ops.on("main"):
             for j in self.mine:
-                r0 = j * self.nb
-                blk = ops.empty(self.N - r0, self._width(j))
-                ops.gram_block(r0, r0, blk)
-                self.cols[j] = blk
-                self.invl[j] = ops.inv_blocks(self._width(j))
+                off, first = self._first_row_at_or_after(j)
+                if first is None:
+                    continue
+                w = self.hgt[j]
+                self.cols[j] = ops.empty(self.H - off, (w + 1) // 2 * 2)    # even leading dimension (16-byte rows)
+                if first == j:
+                    self.invl[j] = ops.inv_blocks(w)
+            nb = self.nb
+            self._bufs = {"row": [ops.empty(max(self.H, 1), nb) for _ in range(2)], "W": [ops.empty(nb, nb) for _ in range(2)],
+                          "eye": ops.eye(nb), "col": None}
+            if self.Pr > 1:
+                cnt = [sum(self.hgt[j] for j in self.mine if j % self.Pr == r2) for r2 in range(self.Pr)]
+                self._bufs["col"] = [[ops.empty(max(c, 1), nb) for c in cnt] for _ in range(2)]
+            self.info = ops.new_info()
+
+    def build_gram(self):
+        ops = self.ops
+        if self._bufs is None:
+            self._alloc()
+        with ops.on("main"):
+            self.info.zero_()
+            for j in self.mine:
+                if j not in self.cols:
+                    continue
+                off, _ = self._first_row_at_or_after(j)
+                w = self.hgt[j]
+                if self.Pr == 1:    # the rows of a block column are contiguous in the matrix: one launch
+                    ops.gram_block(j * self.nb, j * self.nb, self.cols[j][:, :w])
+                    continue
+                for i in self.myrows:
+                    if i >= j:
+                        o = self.roff[i] - off
+                        ops.gram_block(i * self.nb, j * self.nb, self.cols[j][o:o + self.hgt[i], :w])
         self.factored = False
 
     # -- factorisation ------------------------------------------------------------------------------------------------
-    def _update(self, j, k, Pk, which):
-        """A[j nb:, block j] -= P_k[rows of block column j] P_k[rows of block j]^T  (one GEMM, K = w_k)."""
-        off = (j - k) * self.nb
-        rows = Pk[off:]
-        top = Pk[off:off + self._width(j)]
-        self.ops.gemm("NT", rows, top, self.cols[j], -1.0, 1.0, which)
-        self.stats["gemm_flops"] += 2.0 * rows.shape[0] * top.shape[0] * Pk.shape[1]
+    def _panel_factor(self, k):
+        """Ranks of grid column k mod Pc, panel stream: L_kk, W = inv(L_kk) down the column, X_i = A_ik W^T for the
+        owned rows below; X is left in the row-panel buffer k % 2 AND in cols[k] (the factor, needed by solve)."""
+        ops, nb = self.ops, self.nb
+        if k % self.Pc != self.pc:
+            return
+        w = self.hgt[k]
+        diag = (k % self.Pr == self.pr)
+        if diag:
+            blk = self.cols[k][:w, :w]
+            ops.potrf_block(blk, self.invl[k], k * nb, self.info, "panel")
+        if k == self.nblk - 1:
+            return                      # nothing below the last diagonal block
+        W = self._bufs["W"][k % 2]
+        if diag:
+            W.copy_(self._bufs["eye"])
+            ops.trsm(blk, self.invl[k], W, False, "panel")
+        if self.Pr > 1:
+            self._bcast(W, self._grank(k % self.Pr, self.pc), self.col_group)
+        o1, first = self._first_row_at_or_after(k + 1)
+        if first is None:
+            return
+        off_k, _ = self._first_row_at_or_after(k)
+        below = self.cols[k][o1 - off_k:, :w]
+        X = self._bufs["row"][k % 2][:self.H - o1]
+        ops.gemm("NT", below, W, X, 1.0, 0.0, "panel")
+        self.stats["gemm_flops"] += 2.0 * below.shape[0] * w * w
+        below.copy_(X)
+
+    def _distribute(self, k):
+        """All ranks, panel stream: row broadcast of the solved panel rows, then the column operands down the columns."""
+        if k == self.nblk - 1:
+            return
+        o1, first = self._first_row_at_or_after(k + 1)
+        X = self._bufs["row"][k % 2][:self.H - o1]
+        if self.Pc > 1 and first is not None:
+            self._bcast(X, self._grank(self.pr, k % self.Pc), self.row_group)
+        if self.Pr > 1:
+            for r2 in range(self.Pr):
+                blocks = [j for j in self.mine if j > k and j % self.Pr == r2]
+                if not blocks:
+                    continue
+                buf = self._bufs["col"][k % 2][r2][:sum(self.hgt[j] for j in blocks)]
+                if r2 == self.pr:       # this rank holds those block rows in X: pack them
+                    pos = 0
+                    for j in blocks:
+                        buf[pos:pos + self.hgt[j]].copy_(X[self.roff[j] - o1:self.roff[j] - o1 + self.hgt[j]])
+                        pos += self.hgt[j]
+                self._bcast(buf, self._grank(r2, self.pc), self.col_group)
+
+    def _col_operand(self, j, k):
+        """L_jk (h_j x nb) as received at step k."""
+        if self.Pr == 1:
+            o1, _ = self._first_row_at_or_after(k + 1)
+            return self._bufs["row"][k % 2][self.roff[j] - o1:self.roff[j] - o1 + self.hgt[j]]
+        r2 = j % self.Pr
+        pos = sum(self.hgt[q] for q in self.mine if k < q < j and q % self.Pr == r2)
+        return self._bufs["col"][k % 2][r2][pos:pos + self.hgt[j]]
+
+    def _update(self, j, k, which):
+        """Owned blocks of block column j: A_ij -= X_i L_jk^T, i >= j (one GEMM, K = nb)."""
+        if j not in self.cols:
+            return
+        o1, _ = self._first_row_at_or_after(k + 1)
+        oj, first = self._first_row_at_or_after(j)
+        if first is None:
+            return
+        rows = self._bufs["row"][k % 2][oj - o1:self.H - o1]
+        B = self._col_operand(j, k)
+        self.ops.gemm("NT", rows, B, self.cols[j][:, :self.hgt[j]], -1.0, 1.0, which)
+        self.stats["gemm_flops"] += 2.0 * rows.shape[0] * B.shape[0] * self.nb
 
     def factor(self):
-        """Right-looking block-cyclic Cholesky with one-panel look-ahead. Returns LAPACK-style info (0 = ok)."""
-        ops, nb, nblk, world, rank = self.ops, self.nb, self.nblk, self.world, self.rank
-        recv = [None, None]
-        if world > 1:
-            with ops.on("main"):
-                recv = [ops.empty(self.N, nb), ops.empty(self.N, nb)]
-        info = 0
+        """Right-looking 2-D block-cyclic Cholesky with one-panel look-ahead. Returns LAPACK-style info (0 = ok).
+        No host synchronisation inside the loop: INFO is read once at the end."""
+        ops, nblk = self.ops, self.nblk
         ops.record("gram", "main")
         with ops.on("panel"):
             ops.wait("gram", "panel")
-            if owner_of(0, world) == rank:
-                info = ops.potrf_panel(self.cols[0], self.invl[0], "panel")
+            self._panel_factor(0)
         for k in range(nblk):
-            own_k = owner_of(k, world) == rank
-            rows_k = self.N - k * nb
+            nxt_mine = k + 1 < nblk and (k + 1) % self.Pc == self.pc
             with ops.on("panel"):
-                if own_k:
-                    Pk = self.cols[k]
-                else:
-                    ops.wait("main_step_%d" % (k - 2), "panel")  # receive buffer k % 2 was last read at step k - 2
-                    Pk = recv[k % 2][:rows_k, :self._width(k)]
-                self._bcast(Pk, owner_of(k, world))
+                ops.wait("main_step_%d" % (k - 2), "panel")    # the buffers k % 2 were last read at step k - 2
+                self._distribute(k)
                 ops.record("panel_%d" % k, "panel")
-                # look-ahead: block column k + 1 gets this panel first, off the main stream
-                lookahead = k + 1 < nblk and owner_of(k + 1, world) == rank
-                if lookahead:
-                    ops.wait("main_step_%d" % (k - 1), "panel")  # its updates with panels < k ran on the main stream
-                    self._update(k + 1, k, Pk, "panel")
+                if nxt_mine:
+                    # look-ahead: block column k + 1 gets this panel first, off the main stream, and is factored at
+                    # once so that its broadcasts overlap everybody's trailing update
+                    ops.wait("main_step_%d" % (k - 1), "panel")    # its updates with panels < k ran on the main stream
+                    self._update(k + 1, k, "panel")
+                    self._panel_factor(k + 1)
             with ops.on("main"):
                 ops.wait("panel_%d" % k, "main")
                 for j in self.mine:
-                    if j > k + 1:
-                        self._update(j, k, Pk, "main")
+                    if j > k + 1 or (j == k + 1 and not nxt_mine):
+                        self._update(j, k, "main")
                 ops.record("main_step_%d" % k, "main")
-            if lookahead:
-                # factored at once (the call returns when the panel is done; the main stream already holds this
-                # step's trailing update, so the GPU stays busy while the host waits here)
-                with ops.on("panel"):
-                    bad = ops.potrf_panel(self.cols[k + 1], self.invl[k + 1], "panel")
-                if bad and not info:
-                    info = bad + (k + 1) * nb
             ops.forget("main_step_%d" % (k - 2))
             ops.forget("panel_%d" % (k - 1))
-        # A rank that meets a non-SPD panel keeps following the schedule (the failed block is left as it was, so the
+        # A rank that meets a non-SPD block keeps following the schedule (the failed block is left as it was, so the
         # remaining steps compute garbage but nobody hangs in a broadcast); all ranks agree on INFO here.
         ops.synchronize()
-        if world > 1:
-            flag = torch.tensor([info], dtype=torch.int64, device=self._flag_device())
-            dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.group)
+        info = ops.read_info(self.info)
+        if self.world > 1:
+            big = 2 ** 62
+            flag = torch.tensor([info if info > 0 else big], dtype=torch.int64, device=self._flag_device())
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
             info = int(flag.item())
+            info = 0 if info == big else info
         self.factored = info == 0
         if self.factored:
             part = 0.0
             for j in self.mine:
-                part += ops.logdet(self.cols[j][:self._width(j)])
+                if j in self.invl:
+                    part += ops.logdet(self.cols[j][:self.hgt[j], :self.hgt[j]])
             t = torch.tensor([part], dtype=torch.float64, device=self._flag_device())
-            if world > 1:
+            if self.world > 1:
                 dist.all_reduce(t, group=self.group)
             self.logdet = float(t.item())
         return info
@@ -266,49 +433,83 @@ class BlockCyclicGP:
 
     # -- alpha = (K + sigma^2 I)^-1 Y ------------------------------------------------------------------------------
     def solve(self, Y):
-        """Y: N x M host array or tensor (few columns), the same on every rank. Returns alpha (N x M tensor on the ops'
-        device, the same on every rank). Forward: the owner of block column k solves its diagonal block and forms
-        the update of the rows below, broadcasts both ((N - k nb) x M values); backward: the owner reduces against
-        the already known tail and broadcasts x_k (nb x M values)."""
+        """Y: N x M host array or device tensor (few columns), the same on every rank. Returns alpha (N x M tensor on
+        the ops' device, the same on every rank).
+
+        Forward L z = y, block row k: the ranks of grid row k hold the partial sums  sum_{j<k} L_kj z_j  of the blocks
+        they own -> ONE small reduce (nb x M doubles) to the diagonal owner, which solves with L_kk and sends z_k down
+        grid column k, whose ranks add L_ik z_k to their partial sums with one skinny GEMM over the stacked column.
+        Backward L^T x = z mirrors it: the column's ranks form  sum_{i>k} L_ik^T x_i  with one skinny GEMM, reduce down
+        the column, the owner solves with L_kk^T and sends x_k along grid row k. Per block step: at most two
+        collectives of nb x M doubles and a handful of small launches, no host synchronisation, nothing of size
+        (N - k nb) x M is moved; the cost is latency (2 nblk steps), independent of the number of ranks."""
         if not self.factored:
             raise RuntimeError("BlockCyclicGP.solve: factor() first")
-        ops, nb, nblk, world, rank = self.ops, self.nb, self.nblk, self.world, self.rank
-        Yh = Y.detach().cpu().numpy() if isinstance(Y, torch.Tensor) else np.asarray(Y, dtype=np.float64)
-        M = Yh.shape[1]
-        ld = ops.pad_cols(M)
+        ops, nb, nblk = self.ops, self.nb, self.nblk
         with ops.on("main"):
-            b = ops.zeros(self.N, ld)
-            b[:, :M] = ops.from_host(Yh)
-            msg = ops.empty(self.N, ld)
-            # forward: L z = y
+            Yd = ops.from_host(Y)
+            M = Yd.shape[1]
+            ld = ops.pad_cols(M)
+            y = ops.zeros(self.N, ld)
+            y[:, :M].copy_(Yd)
+            acc = ops.zeros(max(self.H, 1), ld)     # stacked over myrows: sum_j L_ij z_j (forward), then x_i (backward)
+            zown = {}                               # z_k on the diagonal owner
+            msg = [ops.zeros(nb, ld) for _ in range(2)]
+            # ---- forward
             for k in range(nblk):
-                r0, w = k * nb, self._width(k)
-                rows = self.N - r0
-                buf = msg[:rows]
-                if owner_of(k, world) == rank:
-                    Lk = self.cols[k]
-                    buf[:w] = b[r0:r0 + w]
-                    ops.trsm(Lk[:w], self.invl[k], buf[:w], False)
-                    if rows > w:
-                        ops.gemm("NN", Lk[w:], buf[:w], buf[w:], 1.0, 0.0)
-                self._bcast(buf, owner_of(k, world))
-                b[r0:r0 + w] = buf[:w]
-                if rows > w:
-                    b[r0 + w:] -= buf[w:]
-            # backward: L^T x = z
+                w = self.hgt[k]
+                in_row, in_col = (k % self.Pr == self.pr), (k % self.Pc == self.pc)
+                diag = in_row and in_col
+                buf = msg[k % 2][:w]
+                if in_row:
+                    part = acc[self.roff[k]:self.roff[k] + w]
+                    if self.Pc > 1:
+                        dist.reduce(part, dst=self._grank(self.pr, k % self.Pc), group=self.row_group)
+                        self.stats["collectives"] += 1
+                    if diag:
+                        torch.sub(y[k * nb:k * nb + w], part, out=buf)
+                        ops.trsm(self.cols[k][:w, :w], self.invl[k], buf, False)
+                        zown[k] = buf.clone()
+                if not in_col or k == nblk - 1:
+                    continue
+                if self.Pr > 1:
+                    self._bcast(msg[k % 2], self._grank(k % self.Pr, self.pc), self.col_group)
+                o1, first = self._first_row_at_or_after(k + 1)
+                if first is not None:
+                    off_k, _ = self._first_row_at_or_after(k)
+                    ops.gemm("NN", self.cols[k][o1 - off_k:, :w], buf, acc[o1:self.H], 1.0, 1.0)
+            # ---- backward: acc now collects x_i for the owned rows
             for k in range(nblk - 1, -1, -1):
-                r0, w = k * nb, self._width(k)
-                rows = self.N - r0
-                buf = msg[:w]
-                if owner_of(k, world) == rank:
-                    Lk = self.cols[k]
-                    buf.copy_(b[r0:r0 + w])
-                    if rows > w:
-                        ops.gemm("TN", Lk[w:], b[r0 + w:], buf, -1.0, 1.0)
-                    ops.trsm(Lk[:w], self.invl[k], buf, True)
-                self._bcast(buf, owner_of(k, world))
-                b[r0:r0 + w] = buf
-        return b[:, :M]
+                w = self.hgt[k]
+                in_row, in_col = (k % self.Pr == self.pr), (k % self.Pc == self.pc)
+                diag = in_row and in_col
+                buf = msg[k % 2][:w]
+                if in_col:
+                    o1, first = self._first_row_at_or_after(k + 1)
+                    if first is not None:
+                        off_k, _ = self._first_row_at_or_after(k)
+                        ops.gemm("TN", self.cols[k][o1 - off_k:, :w], acc[o1:self.H], buf, 1.0, 0.0)
+                    else:
+                        buf.zero_()
+                    if self.Pr > 1:
+                        dist.reduce(msg[k % 2], dst=self._grank(k % self.Pr, self.pc), group=self.col_group)
+                        self.stats["collectives"] += 1
+                    if diag:
+                        torch.sub(zown[k], buf, out=buf)
+                        ops.trsm(self.cols[k][:w, :w], self.invl[k], buf, True)
+                if in_row:
+                    if self.Pc > 1:
+                        self._bcast(msg[k % 2], self._grank(self.pr, k % self.Pc), self.row_group)
+                    acc[self.roff[k]:self.roff[k] + w].copy_(buf)
+            # ---- every rank gets the whole alpha: each block row is contributed by grid column 0 of its grid row
+            out = ops.zeros(self.N, ld)
+            if self.pc == 0:
+                for i in self.myrows:
+                    out[i * nb:i * nb + self.hgt[i]].copy_(acc[self.roff[i]:self.roff[i] + self.hgt[i]])
+            if self.Pr > 1:     # with Pr = 1 every rank already holds every block row
+                dist.all_reduce(out, group=self.group)
+                self.stats["collectives"] += 1
+        return out[:, :M]
 
     def learn(self, Y):
         """Gram + factorisation + solve; returns (alpha, logdet, info)."""

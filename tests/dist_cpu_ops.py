@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE: a numpy stand-in for gpr_b200.dist.DeviceOps so that the multi-GPU host logic (ownership,
-schedule, look-ahead ordering, collectives) runs under gloo on CPU with world_size 2. Block operations are plain
-numpy/scipy on CPU tensors; the kernel matrix comes from the oracle. Never imported by the product."""
+2-D schedule, look-ahead ordering, collectives) runs under gloo on CPU with world_size 2, 3 and 4. Block operations are
+plain numpy/scipy on CPU tensors; the kernel matrix comes from the oracle. Never imported by the product."""
 import contextlib
 
 import numpy as np
@@ -19,14 +19,29 @@ class CpuOps:
         self.sigma = float(sigma)
         self.log = []  # (stream, op) trace, lets tests assert the schedule
 
+    def set_samples(self, X, sigma):
+        self.X = np.ascontiguousarray(X, dtype=np.float64)
+        self.sigma = float(sigma)
+
     def empty(self, rows, cols):
         return torch.full((rows, cols), float("nan"), dtype=torch.float64)
 
     def zeros(self, rows, cols):
         return torch.zeros((rows, cols), dtype=torch.float64)
 
+    def eye(self, n):
+        return torch.eye(n, dtype=torch.float64)
+
     def from_host(self, a):
+        if isinstance(a, torch.Tensor):
+            return a
         return torch.as_tensor(np.ascontiguousarray(a, dtype=np.float64))
+
+    def new_info(self):
+        return torch.zeros(1, dtype=torch.int32)
+
+    def read_info(self, info):
+        return int(info.item())
 
     @contextlib.contextmanager
     def on(self, which):
@@ -48,18 +63,21 @@ class CpuOps:
             K[i - row0, i - col0] += self.sigma ** 2
         out.copy_(torch.as_tensor(K))
 
-    def potrf_panel(self, P, invL, which="panel"):
+    def potrf_block(self, P, invL, col0, info, which="panel"):
         self.log.append((which, "potrf", tuple(P.shape)))
         w = P.shape[1]
-        A = P[:w].numpy()
+        A = P[:w].numpy().copy()
+        S = np.tril(A) + np.tril(A, -1).T
         try:
-            L = np.linalg.cholesky(np.tril(A) + np.tril(A, -1).T)
+            L = np.linalg.cholesky(S)
         except np.linalg.LinAlgError:
-            return 1
+            if int(info.item()) == 0:           # LAPACK INFO: order of the first leading minor that is not SPD
+                bad = next(j for j in range(1, w + 1) if np.linalg.eigvalsh(S[:j, :j]).min() <= 0)
+                info.fill_(col0 + bad)
+            return
         P[:w] = torch.as_tensor(np.tril(L) + np.triu(A, 1))
         if P.shape[0] > w:
             P[w:] = torch.as_tensor(sla.solve_triangular(L, P[w:].numpy().T, lower=True).T)
-        return 0
 
     def gemm(self, form, A, B, Cm, alpha, beta, which="main"):
         self.log.append((which, "gemm" + form, tuple(Cm.shape)))

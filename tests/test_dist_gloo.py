@@ -25,7 +25,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, N, nb, M, kname, out):
+def _worker(rank, world, port, N, nb, M, kname, out, grid=None):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -35,8 +35,14 @@ def _worker(rank, world, port, N, nb, M, kname, out):
         from oracle import gpr_oracle as orc
         X, Y = make_problem(N, 3, M, seed=11)
         ops = CpuOps(KERNELS[kname], X, 1.0)
-        gp = gd.BlockCyclicGP(ops, N, nb=nb)
-        assert gp.mine == list(range(rank, gp.nblk, world))
+        gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid)
+        if grid is None:
+            assert gp.mine == list(range(rank, gp.nblk, world))
+        else:   # every block (i, j), i >= j, has exactly one owner and this rank holds exactly its own
+            pr, pc = divmod(rank, grid[1])
+            assert gp.mine == [j for j in range(gp.nblk) if j % grid[1] == pc]
+            assert gp.myrows == [i for i in range(gp.nblk) if i % grid[0] == pr]
+            assert all(gd.block_owner(i, j, *grid) == rank for j in gp.mine for i in gp.myrows if i >= j)
         alpha, logdet, info = gp.learn(Y)
         assert info == 0
         o = orc.OracleGP(KERNELS[kname], X, Y, 1.0)
@@ -48,7 +54,11 @@ def _worker(rank, world, port, N, nb, M, kname, out):
         potrf_streams = {s for s, op, *_ in ops.log if op == "potrf"}
         main_ops = {op for s, op, *_ in ops.log if s == "main"}
         res = {"err": err, "logdet_err": abs(logdet - ld_ref) / abs(ld_ref), "potrf_streams": sorted(potrf_streams),
-               "main_has_potrf": "potrf" in main_ops, "bcast_bytes": gp.stats["bcast_bytes"]}
+               "main_has_potrf": "potrf" in main_ops, "bcast_bytes": gp.stats["bcast_bytes"],
+               "collectives": gp.stats["collectives"]}
+        # a second Learn on the same object (buffers are reused) gives the same answer
+        alpha2, _, info2 = gp.learn(Y)
+        res["relearn_same"] = bool(info2 == 0 and torch.equal(alpha2, alpha))
         # every rank must hold the same alpha
         t = alpha.clone()
         dist.broadcast(t, src=0)
@@ -59,18 +69,33 @@ def _worker(rank, world, port, N, nb, M, kname, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,N,nb,M,kname", [(2, 700, 128, 3, "sum3"), (3, 1000, 256, 1, "rq"), (2, 256, 128, 2, "gaussian")])
+@pytest.mark.parametrize("world,N,nb,M,kname", [(2, 700, 128, 3, "sum3"), (3, 1000, 256, 1, "rq")])
 def test_block_cyclic_learn_matches_oracle(tmp_path, world, N, nb, M, kname):
     out = str(tmp_path / "res.pt")
     mp.spawn(_worker, args=(world, _free_port(), N, nb, M, kname, out), nprocs=world, join=True)
     res = torch.load(out)
     assert res["err"] <= 1e-9, res          # alpha vs the oracle's LU-inverse path (tolerance of BASELINE.json)
     assert res["logdet_err"] <= 1e-10, res
-    assert res["same_alpha"]
+    assert res["same_alpha"] and res["relearn_same"]
     assert res["potrf_streams"] == ["panel"] and not res["main_has_potrf"]
     nblk = (N + nb - 1) // nb
-    expect = sum((N - k * nb) * min(nb, N - k * nb) * 8 for k in range(nblk))
+    expect = sum((N - (k + 1) * nb) * nb * 8 for k in range(nblk - 1))   # every panel below its diagonal block, once
     assert res["bcast_bytes"] >= expect  # factor broadcasts (+ the solve's small messages)
+
+
+@pytest.mark.parametrize("world,grid,N,nb,M,kname", [
+    (2, (2, 1), 700, 128, 2, "sum3"),          # column communicator only
+    (4, (2, 2), 1001, 128, 3, "rq"),           # the 2 x 2 schedule, ragged AND odd last block (1001 = 7 * 128 + 105)
+    (4, (1, 4), 900, 128, 1, "prod"),          # the degenerate 1 x g layout on the same code path
+])
+def test_two_dimensional_grid_matches_oracle(tmp_path, world, grid, N, nb, M, kname):
+    out = str(tmp_path / "res.pt")
+    mp.spawn(_worker, args=(world, _free_port(), N, nb, M, kname, out, grid), nprocs=world, join=True)
+    res = torch.load(out)
+    assert res["err"] <= 1e-9, res
+    assert res["logdet_err"] <= 1e-10, res
+    assert res["same_alpha"] and res["relearn_same"]
+    assert res["potrf_streams"] == ["panel"] and not res["main_has_potrf"]
 
 
 def test_single_process_block_cyclic_equals_oracle():
@@ -111,3 +136,28 @@ def test_non_spd_matrix_reports_info_on_every_rank():
     assert gp.factor() > 128
     with pytest.raises(RuntimeError):
         gp.solve(Y)
+
+
+def _bad_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from gpr_b200 import dist as gd
+        from tests.dist_cpu_ops import CpuOps
+        X, Y = make_problem(512, 2, 1, seed=2)
+        gp = gd.BlockCyclicGP(CpuOps(KERNELS["gaussian"], X, 1.0), 512, nb=128, grid=(2, 2))
+        gp.build_gram()
+        if 2 in gp.invl:    # the owner of diagonal block 2 makes it indefinite; nobody else knows until the end
+            gp.cols[2][:128, :128] -= 50.0 * torch.eye(128, dtype=torch.float64)
+        info = gp.factor()  # must return on every rank (no hang in a broadcast) with the same INFO
+        torch.save(info, out + ".%d" % rank)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_non_spd_block_on_a_2x2_grid_gives_every_rank_the_same_info(tmp_path):
+    out = str(tmp_path / "info")
+    mp.spawn(_bad_worker, args=(4, _free_port(), out), nprocs=4, join=True)
+    infos = [torch.load(out + ".%d" % r) for r in range(4)]
+    assert len(set(infos)) == 1 and 256 < infos[0] <= 384, infos
