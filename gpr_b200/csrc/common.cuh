@@ -85,8 +85,8 @@ struct Ctx {
     cudaStream_t panel_stream = nullptr;  // high-priority stream for the look-ahead panel
     cudaStream_t aux_stream = nullptr;    // off-critical-path part of a panel step (potrf.cu: factor_panel)
     cudaEvent_t ev_pcrit = nullptr, ev_paux = nullptr;
-    int64_t opt_panel_split = 0;          // 1: only the next block column is updated on the panel's critical stream
-    int64_t opt_gemm_small = 0;           // 1: 32 x 128 CTA tiles for N <= 128, K <= 256 products (panel solves)
+    int64_t opt_panel_split = 1;          // 1: only the next block column is updated on the panel's critical stream
+    int64_t opt_gemm_small = 1;           // 1: 32 x 128 CTA tiles for N <= 128, K <= 256 products (panel solves)
     int64_t opt_profile = 0;      // time every trailing-update GEMM launch with CUDA events (bench.py roofline)
     double prof_tb_ms = 0.0, prof_tb_flops = 0.0, prof_tb_launches = 0.0;  // last factorisation
     double prof_gemv_ms = 0.0, prof_gemv_bytes = 0.0, prof_gemv_launches = 0.0;  // accumulated since reset

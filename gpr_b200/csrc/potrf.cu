@@ -797,8 +797,9 @@ int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* i
     GP_CUDA(c, cudaFuncSetAttribute(potrf_tile3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P3_SMEM));
     GP_CUDA(c, cudaMemsetAsync(c->dInfo, 0, sizeof(int), c->stream));
     int64_t NBO = c->opt_nbo;
-    // measured on B200 (tools/chol_sweep2.py): 256 wins at N = 8192, 512 at 16384, 768-1024 from 24576
-    if (NBO <= 0) NBO = (N <= 10240) ? 256 : ((N <= 20480) ? 512 : 1024);
+    // measured on B200 with the round-2 panel (tools/nbo_sweep.py; DMMA tile, 32 x 128 panel GEMMs, split panel step):
+    // 384 wins at N = 8192 (9.19 ms), 768 at 12288-16384 (23.7 / 50.7 ms), 1024 from 24576 (158.7 / 364.3 ms)
+    if (NBO <= 0) NBO = (N <= 10240) ? 384 : ((N <= 20480) ? 768 : 1024);
     if (NBO < NB) NBO = NB;
     NBO = NBO / NB * NB;
     if (c->opt_chol_left && c->panel_stream && N > 2 * NBO) {

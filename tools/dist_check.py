@@ -1,4 +1,4 @@
-"""torchrun --nproc-per-node G tools/dist_check.py [N] [nb]: block-cyclic Learn on G GPUs vs the single-GPU library
+"""torchrun --nproc-per-node G tools/dist_check.py [N] [nb] [PrxPc]: block-cyclic Learn on G GPUs vs the single-GPU library
 (same inputs; results must agree), with device timings (max over ranks)."""
 import json, os, sys, time
 import numpy as np
@@ -15,6 +15,7 @@ KS = "SumKernel(SumKernel(GaussianKernel(2,1,),PeriodicKernel(1,2,1,)),WhiteKern
 def main():
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
     nb = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
+    grid = tuple(int(v) for v in sys.argv[3].split("x")) if len(sys.argv) > 3 else None
     rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(local)
     if world > 1:
@@ -24,7 +25,7 @@ def main():
     Y = (np.sin(3 * X[:, :1]) + 0.1 * rng.standard_normal((N, 1)))
     ops_, params = gpr_b200.KernelFactory.GetKernel(KS).lower()
     ops = gd.DeviceOps(local, ops_, params, X, 1.0)
-    gp = gd.BlockCyclicGP(ops, N, nb=nb)
+    gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid)
     out = {}
     for it in range(2):
         if world > 1:
@@ -37,7 +38,8 @@ def main():
         tm = torch.tensor([t1 - t0, t2 - t1, t3 - t2], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-        out = {"N": N, "nb": nb, "world": world, "info": info, "gram_s": tm[0].item(), "factor_s": tm[1].item(),
+        out = {"N": N, "nb": nb, "world": world, "grid": "%dx%d" % (gp.Pr, gp.Pc), "info": info,
+               "collectives": gp.stats["collectives"], "bcast_GB": gp.stats["bcast_bytes"] * 1e-9, "gram_s": tm[0].item(), "factor_s": tm[1].item(),
                "solve_s": tm[2].item(), "factor_TFs_total": N ** 3 / 3.0 / tm[1].item() * 1e-12, "logdet": gp.logdet}
     if rank == 0 and N <= 32768:
         h = gpr_b200.Handle(local)
