@@ -201,17 +201,101 @@ def run_gpu(args):
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    env = {"torch": torch, "gpr_b200": gpr_b200, "rank": rank, "local_rank": local_rank, "world": world, "dev": dev,
+           "dist": dist, "barrier": barrier, "max_over_ranks": max_over_ranks, "sum_over_ranks": sum_over_ranks}
+    detail = {}
+    if world == 1:
+        line = headline_c3(args, env, detail)
+    else:
+        line = headline_c5(args, env, detail)
+        if not args.skip_replicas:
+            rep = headline_c3(args, env, {}, steps=min(args.steps, 3), warmup=3, checks=False)
+            if rank == 0:
+                detail["replicas"] = rep
+                line["config"]["replicas"] = {"what": "one independent C3 model per GPU, no collective (the round-1 headline)",
+                                              "tflops_total": rep["value"], "ms_per_step": rep["ms_per_step"]}
+    torch.cuda.empty_cache()
+
+    predict = None if args.skip_predict else run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier,
+                                                         max_over_ranks)
+    if predict and rank == 0:
+        detail["predict"] = predict
+        line["config"]["predict"] = {"workload": predict["config"]["workload"], "M": predict["config"]["M"],
+                                     "predictions_per_s": predict["value"], "e2e_predictions_per_s": predict["e2e"]["value"],
+                                     "hbm_gbs": predict["roofline"]["achieved"], "hbm_frac": predict["roofline"]["frac"],
+                                     "sharding": "alpha columns M / %d per GPU, no collective" % world}
+    if not args.skip_predict_ci:
+        pci = run_predict_ci(args, env)
+        if pci and rank == 0:
+            detail["predict_ci"] = pci
+            line["config"]["predict_ci"] = {k: pci[k] for k in ("points_per_s", "ms_per_point_t1", "T", "N", "sharding")}
+    if world > 1 and not args.skip_loglik:
+        sl = run_sharded_loglik(args, env)
+        if sl and rank == 0:
+            detail["loglik_sharded"] = sl
+            line["config"]["loglik_sharded"] = {k: sl[k] for k in ("iteration_ms", "N", "collective", "grad_vs_1gpu")}
+    if rank == 0 and world == 1:
+        for name, flag, fn in (("loglik", args.skip_loglik, run_loglik), ("pca_frame", args.skip_pca, run_pca),
+                               ("host_io", args.skip_hostio, run_host_io), ("sparse", args.skip_sparse, run_sparse)):
+            if not flag:
+                detail[name] = fn(torch, gpr_b200, local_rank)
+        if "loglik" in detail:
+            line["config"]["loglik_iteration_ms"] = detail["loglik"]["value"]
+            line["config"]["loglik_phase_ms"] = detail["loglik"]["phase_ms"]
+        if not args.skip_cpu:
+            line["cpu_baseline"] = run_cpu_baseline()
+    if rank == 0:
+        peaks = measured_peaks()
+        if peaks:
+            line["measured_peaks"] = {"hbm_gbs": peaks.get("hbm_gbs")}
+        # the contract line stays compact (the driver keeps `config` and `roofline`); the full sub-objects go to stderr
+        # and, when the directory exists, to gpurun_out/bench_detail_<n>gpu.json
+        sys.stderr.write("bench detail: " + json.dumps(detail) + "\n")
+        try:
+            if os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+                json.dump({"line": line, "detail": detail},
+                          open(os.path.join(ROOT, "gpurun_out", "bench_detail_%dgpu.json" % world), "w"), indent=1)
+        except Exception:
+            pass
+        print(json.dumps(line))
+        sys.stdout.flush()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def oracle_rows(kernel_string, X, rows, chunk=16):
+    """k(x_r, x_j) for the sampled rows on the CPU (numpy restatement of include/Kernel.h, pinned to oracle/_ref): the
+    checker's side of the residual checks, independent of the device kernel functor."""
+    from oracle import gpr_oracle as orc
+    k = orc.parse_kernel(kernel_string)
+    return np.concatenate([orc.kernel_matrix(k, X[rows[i:i + chunk]], X) for i in range(0, len(rows), chunk)], axis=0)
+
+
+def residual_rows(kernel_string, X, Y, alpha, sigma, nrows=192, seed=5):
+    """max |K_r alpha + sigma^2 alpha_r - y_r| / max |y| over sampled rows r, kernel rows from the oracle."""
+    rng = np.random.default_rng(seed)
+    rows = np.sort(rng.choice(X.shape[0], nrows, replace=False))
+    Kr = oracle_rows(kernel_string, X, rows)
+    r = Kr @ alpha + sigma * sigma * alpha[rows] - Y[rows]
+    return float(np.abs(r).max() / np.abs(Y).max())
+
+
+def headline_c3(args, env, detail, steps=None, warmup=None, checks=True):
+    """C3 Learn on every rank (at 1 GPU: the headline; at N > 1: the independent-replica sub-object)."""
+    torch, gpr_b200 = env["torch"], env["gpr_b200"]
+    rank, local_rank, world, dev = env["rank"], env["local_rank"], env["world"], env["dev"]
+    steps = steps or args.steps
+    warmup = warmup or args.warmup
     N, d, M = args.n, C3_D, C3_M
     kernel = gpr_b200.KernelFactory.GetKernel(C3_KERNEL)
     ops, params = kernel.lower()
-    # every rank learns its own model: same shape, different data and hyper-parameter point
     params = list(params)
-    params[0] *= 1.0 + 0.01 * rank
+    params[0] *= 1.0 + 0.01 * rank          # every rank learns its own model: different data and hyper-parameter point
     Xh, Yh = c3_inputs(N, seed=rank)
-    Xp = torch.from_numpy(Xh).pin_memory()
-    Yp = torch.from_numpy(Yh).pin_memory()
-    Xd, Yd = Xp.to(dev), Yp.to(dev)
-    alpha_host = torch.empty(N, M, dtype=torch.float64).pin_memory()
+    Xd, Yd = torch.from_numpy(Xh).to(dev), torch.from_numpy(Yh).to(dev)
+    alpha_host = np.empty((N, M))            # pageable, as the reference API's own Eigen storage
 
     h = gpr_b200.Handle(local_rank)
     stream = torch.cuda.current_stream(dev)
@@ -219,18 +303,16 @@ def run_gpu(args):
     h.set_kernel(ops, params)
     h.set_option("profile", 1)
     h.set_train_dev(Xd.data_ptr(), N, d, Yd.data_ptr(), M, C3_SIGMA)
-
-    # ---- device-resident Learn: value ---------------------------------------------------------------
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         h.learn(0)
-    barrier()
+    env["barrier"]()
     sampler = ClockSampler(local_rank)
     l0 = h.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     phases = {"gram": 0.0, "potrf": 0.0, "solve": 0.0}
     tb_ms = tb_flops = tb_launches = 0.0
     e0.record(stream)
-    for _ in range(args.steps):
+    for _ in range(steps):
         h.learn(0)
         ms = h.phase_ms()
         for k in phases:
@@ -239,138 +321,214 @@ def run_gpu(args):
         tb_flops += h.get_stat("tb_flops")
         tb_launches += h.get_stat("tb_launches")
     e1.record(stream)
-    barrier()
+    env["barrier"]()
     launches = h.launch_count() - l0
     clocks = sampler.stop()
-    elapsed_ms = max_over_ranks(e0.elapsed_time(e1))
-    value = world * learn_flops(N, M) * args.steps / elapsed_ms * 1e-9
+    elapsed_ms = env["max_over_ranks"](e0.elapsed_time(e1))
+    value = world * learn_flops(N, M) * steps / elapsed_ms * 1e-9
     alpha_dev_check = h.alpha()
 
-    # ---- end to end through the host-pointer C-ABI: pinned host X, Y -> alpha on the host -------------
-    Xn, Yn = Xp.numpy(), Yp.numpy()
-    for _ in range(min(args.warmup, 2)):
-        h.set_train(Xn, Yn, C3_SIGMA)
+    # end to end through the host-pointer C-ABI: PAGEABLE host X, Y (what the reference API owns) -> alpha on the host
+    e2e_steps = steps
+    for _ in range(2):
+        h.set_train(Xh, Yh, C3_SIGMA)
         h.learn(0)
-        h.lib.gprb200_get_alpha(h.h, alpha_host.data_ptr())
-    barrier()
+        h.lib.gprb200_get_alpha(h.h, alpha_host.ctypes.data)
+    env["barrier"]()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        h.set_train(Xn, Yn, C3_SIGMA)                         # H2D of this step's inputs
+    for _ in range(e2e_steps):
+        h.set_train(Xh, Yh, C3_SIGMA)                              # H2D of this step's inputs
         h.learn(0)
-        h.lib.gprb200_get_alpha(h.h, alpha_host.data_ptr())   # D2H of the result
+        h.lib.gprb200_get_alpha(h.h, alpha_host.ctypes.data)       # D2H of the result
     torch.cuda.synchronize()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
-    barrier()
-    e2e_value = world * learn_flops(N, M) * args.steps / e2e_ms * 1e-9
-    e2e_ok = bool(np.allclose(alpha_host.numpy(), alpha_dev_check, rtol=1e-9, atol=1e-12))
-    total_launches = int(sum_over_ranks(launches))
-
-    # residual-based parity at full size (size-independent property): ||(K + s^2 I) alpha - y|| / ||y||
+    e2e_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3)
+    env["barrier"]()
+    e2e_value = world * learn_flops(N, M) * e2e_steps / e2e_ms * 1e-9
+    e2e_ok = bool(np.allclose(alpha_host, alpha_dev_check, rtol=1e-9, atol=1e-12))
+    total_launches = int(env["sum_over_ranks"](launches))
     resid = None
-    if rank == 0 and not args.skip_checks:
-        resid = residual_check(torch, gpr_b200, h, Xd, Yd, N, dev)
+    if rank == 0 and checks and not args.skip_checks:
+        resid = {"rel_residual_rows": residual_rows(kernel_string_with(params), Xh, Yh, alpha_host, C3_SIGMA),
+                 "note": "max |K_r alpha + s^2 alpha_r - y_r| / max |y| on 192 sampled rows of the N=%d problem, kernel rows "
+                         "evaluated by the CPU oracle (not by the device functor)" % N}
+    gram = None
+    if rank == 0 and checks:
+        gram = gram_evidence(torch, h, N, d, phases["gram"] / steps, dev)
     h.close()
     del Xd, Yd
     torch.cuda.empty_cache()
+    chol_tf = N ** 3 / 3.0 / (phases["potrf"] / steps) * 1e-9
+    line = {
+        "metric": "gp_learn_fp64_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world,
+        "steps": steps, "warmup": warmup, "ms_per_step": elapsed_ms / steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {
+            "workload": C3_WORKLOAD, "N": N, "d": d, "M": M, "models_per_step": world,
+            "useful_flops_per_model": learn_flops(N, M),
+            "l2": "inputs larger than L2 (K is %.1f GB)" % (8.0 * N * N * 1e-9),
+            "parallelism": "one independent model per GPU, no collective" if world > 1 else "single GPU",
+            "learn_s": elapsed_ms / steps * 1e-3, "cholesky_tflops": chol_tf,
+            "phase_ms": {k: v / steps for k, v in phases.items()},
+        },
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": int(8 * N * (d + M)),
+                "d2h_bytes_per_step": int(8 * N * M), "ms_per_step": e2e_ms / e2e_steps, "matches_device_run": e2e_ok,
+                "host_buffers": "pageable numpy arrays"},
+        "gpu_launches": total_launches,
+        "roofline": {
+            "kernel": "dgemm_kernel<128,64,64,16,NT,3 stages> (SYRK trailing update of the blocked Cholesky, DMMA.8x8x4)",
+            "bound": "tensor", "achieved": tb_flops / tb_ms * 1e-9 if tb_ms else None, "peak": FP64_PEAK_TFLOPS,
+            "unit": "TFLOP/s", "frac": (tb_flops / tb_ms * 1e-9 / FP64_PEAK_TFLOPS) if tb_ms else None,
+            "traffic": TRAFFIC_TB_BYTES_PER_LAUNCH,
+            "traffic_note": "ncu --set full of the largest launch T^b(0): 7.61 GB read + 3.76 GB written vs 7.79 GB "
+                            "algorithmic (profiles/r01b_ncu_summary.md)",
+            "launches": tb_launches, "avg_launch_ms": tb_ms / tb_launches if tb_launches else None,
+            "share_of_step": tb_ms / elapsed_ms if elapsed_ms else None,
+            "peak_source": "FP64 is absent from MEASURED_PEAKS.json; 37.1 = measured DMMA issue rate on this pool "
+                           "(profiles/r01_fp64_probe.txt); cuBLAS DGEMM measured 36.2",
+            "cholesky_frac_of_peak": chol_tf / FP64_PEAK_TFLOPS,
+        },
+        "residual": resid,
+    }
+    if gram:
+        line["config"]["gram"] = gram
+    return line
 
-    predict = None if args.skip_predict else run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier,
-                                                         max_over_ranks)
 
-    loglik = None
-    if rank == 0 and not args.skip_loglik:
-        loglik = run_loglik(torch, gpr_b200, local_rank)
+def kernel_string_with(params):
+    """C3 kernel string with the given parameter vector (order: Gaussian sigma, scale; Periodic scale, b, sigma; White)."""
+    p = [repr(float(v)) for v in params]
+    return "SumKernel(SumKernel(GaussianKernel(%s,%s,),PeriodicKernel(%s,%s,%s,)),WhiteKernel(%s,))" % tuple(p)
 
-    pca = None
-    if rank == 0 and not args.skip_pca:
-        pca = run_pca(torch, gpr_b200, local_rank)
 
-    host_io = None
-    if rank == 0 and not args.skip_hostio:
-        host_io = run_host_io(torch, gpr_b200, local_rank)
-    sparse = None
-    if rank == 0 and not args.skip_sparse:
-        sparse = run_sparse(torch, gpr_b200, local_rank)
+def gram_evidence(torch, h, N, d, learn_gram_ms, dev):
+    """Achieved HBM write GB/s of the Gram paths the API runs (north_star subsystem 1): the lower-triangle build inside
+    Learn and the SYMMETRIC full-K build of ComputeKernelMatrix (gprb200_gram_dev: N^2/2 pairs evaluated, mirrored)."""
+    peaks = measured_peaks() or {}
+    hbm = peaks.get("hbm_gbs", HBM_FALLBACK_GBS)
+    ldk = (N + 15) // 16 * 16
+    K = torch.empty(N, ldk, dtype=torch.float64, device=dev)
+    out = {"learn_lower_triangle": {"ms": learn_gram_ms, "bytes": 4.0 * N * N, "gbs": 4.0 * N * N / learn_gram_ms * 1e-6,
+                                    "frac_of_hbm": 4.0 * N * N / learn_gram_ms * 1e-6 / hbm}}
+    for _ in range(2):
+        h._ck(h.lib.gprb200_gram_dev(h.h, K.data_ptr(), ldk, 1))
+    t = []
+    for _ in range(3):
+        h._ck(h.lib.gprb200_gram_dev(h.h, K.data_ptr(), ldk, 1))
+        t.append(h.phase_ms()["gram"])
+    ms = min(t)
+    out["symmetric_full_K"] = {"kernel": "C3 Sum(Sum(Gaussian,Periodic),White)", "ms": ms, "bytes": 8.0 * N * N,
+                               "gbs": 8.0 * N * N / ms * 1e-6, "frac_of_hbm": 8.0 * N * N / ms * 1e-6 / hbm}
+    del K
+    return out
 
-    large = None
-    if world > 1 and not args.skip_large:
-        large = run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist)
 
-    cpu_baseline = None
-    if rank == 0 and world == 1 and not args.skip_cpu:
-        cpu_baseline = run_cpu_baseline()
-
-    if rank == 0:
-        peaks = measured_peaks()
-        line = {
-            "metric": "gp_learn_fp64_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {
-                "workload": "C3: GP Learn (Gram + Cholesky + solve), Sum(Sum(Gaussian,Periodic),White), d=8, M=1, fp64",
-                "N": N, "models_per_step": world, "useful_flops_per_model": learn_flops(N, M),
-                "l2": "inputs larger than L2 (K is %.1f GB)" % (8.0 * N * N * 1e-9),
-                "parallelism": "one independent model per GPU, no collective" if world > 1 else "single GPU",
-            },
-            "learn_s": elapsed_ms / args.steps * 1e-3,
-            "cholesky_tflops": N ** 3 / 3.0 / (phases["potrf"] / args.steps) * 1e-9,
-            "phase_ms": {k: v / args.steps for k, v in phases.items()},
-            "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": int(8 * N * (d + M)),
-                    "d2h_bytes_per_step": int(8 * N * M), "ms_per_step": e2e_ms / args.steps,
-                    "matches_device_run": e2e_ok},
-            "gpu_launches": total_launches,
-            "roofline": {
-                "kernel": "dgemm_kernel<128,64,64,16,NT,3 stages> (SYRK trailing update of the blocked Cholesky, "
-                          "DMMA.8x8x4, 16 warps/SM)",
-                "bound": "tensor", "achieved": tb_flops / tb_ms * 1e-9 if tb_ms else None, "peak": FP64_PEAK_TFLOPS,
-                "unit": "TFLOP/s", "frac": (tb_flops / tb_ms * 1e-9 / FP64_PEAK_TFLOPS) if tb_ms else None,
-                "traffic": TRAFFIC_TB_BYTES_PER_LAUNCH,
-                "traffic_note": "ncu capture of the largest launch T^b(0) (31744^2/2 by K=1024, 28.62 ms): 7.61 GB read "
-                                "+ 3.76 GB written against 7.79 GB algorithmic (panel + C read + C write); "
-                                "profiles/r01b_ncu_summary.md",
-                "launches": tb_launches, "avg_launch_ms": tb_ms / tb_launches if tb_launches else None,
-                "share_of_step": tb_ms / (elapsed_ms) if elapsed_ms else None,
-                "peak_source": "FP64 is absent from MEASURED_PEAKS.json; 37.1 = measured DMMA issue rate on this pool "
-                               "(profiles/r01_fp64_probe.txt); cuBLAS DGEMM measured 36.2",
-                "cholesky_frac_of_peak": N ** 3 / 3.0 / (phases["potrf"] / args.steps) * 1e-9 / FP64_PEAK_TFLOPS,
-            },
-            "residual": resid,
-        }
-        gram_ms = phases["gram"] / args.steps
-        hbm_peak = (peaks or {}).get("hbm_gbs", 6650.0)
-        # C3 kernel per pair: 2d (difference, square) + 2d (PERIODIC trig-feature dot product) + 2 x ~20 (two exponentials) + ~5
-        gram_fp64_per_pair = 2 * d + 2 * d + 2 * 20 + 5
-        gram_floor_ms = (N * (N + 1) / 2.0) * gram_fp64_per_pair / (FP64_PEAK_TFLOPS / 2.0 * 1e12) * 1e3
-        line["gram"] = {
-            "kernel": "gram_rows_kernel<1> (term form, lower triangle only, 4 N^2 bytes written)",
-            "ms": gram_ms, "bytes_written": 4.0 * N * N, "achieved_gbs": 4.0 * N * N / gram_ms * 1e-6,
-            "frac_of_hbm_peak": 4.0 * N * N / gram_ms * 1e-6 / hbm_peak, "bound": "fp64 alu",
-            "fp64_instr_per_pair": gram_fp64_per_pair, "fp64_floor_ms": gram_floor_ms,
-            "frac_of_fp64_floor": gram_floor_ms / gram_ms if gram_ms else None,
-            "note": "FP64-ALU-bound, not HBM-bound, for this kernel family at d = 8: the DFMA pipe (half of the 37.1 TFLOP/s "
-                    "FMA rate counted as instructions) needs fp64_floor_ms; HBM would need %.2f ms" % (4.0 * N * N / hbm_peak * 1e-6),
-        }
-        if predict:
-            line["predict"] = predict
-        if large:
-            line["large_n"] = large
-        if loglik:
-            line["loglik"] = loglik
-        if pca:
-            line["pca_frame"] = pca
-        if sparse:
-            line["sparse"] = sparse
-        if host_io:
-            line["host_io"] = host_io
-        if cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline
-        if peaks:
-            line["measured_peaks"] = {"hbm_gbs": peaks.get("hbm_gbs")}
-        print(json.dumps(line))
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
-    return 0
+def headline_c5(args, env, detail):
+    """N > 1 GPUs: ONE model of N = 131072 samples (BASELINE config C5; K = 137 GB) over all ranks - Gram in the
+    factorisation's layout, 2-D block-cyclic Cholesky with NCCL panel broadcasts, distributed solve (gpr_b200/dist.py).
+    Strong scaling: the problem is fixed, value = useful flops / time (max over ranks, CUDA events)."""
+    torch, gpr_b200, dist = env["torch"], env["gpr_b200"], env["dist"]
+    rank, local_rank, world, dev = env["rank"], env["local_rank"], env["world"], env["dev"]
+    from gpr_b200 import dist as gd
+    N, nb, M = args.large_n, args.large_nb, C3_M
+    grid = tuple(int(v) for v in args.grid.split("x")) if args.grid else gd.default_grid(world)
+    rng = np.random.default_rng(SEED + 131)
+    X = rng.uniform(-1, 1, (N, C3_D))
+    Y = (np.sin(3.0 * X[:, :1]) + 0.5 * np.cos(2.0 * X[:, 1:2] + X[:, 2:3]) + 0.1 * rng.standard_normal((N, 1)))
+    ops_, params = gpr_b200.KernelFactory.GetKernel(C3_KERNEL).lower()
+    ops = gd.DeviceOps(local_rank, ops_, params, X, C3_SIGMA)
+    warm = gd.BlockCyclicGP(ops, 8192, nb=nb, grid=grid)     # communicators, allocator, kernel attributes
+    warm.learn(Y[:8192])
+    del warm
+    torch.cuda.empty_cache()
+    gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid)
+    Yd = torch.from_numpy(Y).to(dev)
+    for _ in range(1 if args.large_quick_warmup else args.warmup):
+        gp.learn(Yd)
+    env["barrier"]()
+    sampler = ClockSampler(local_rank)
+    l0 = ops.h.launch_count() + ops.hp.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    tsum = np.zeros(4)
+    info, alpha = 0, None
+    for _ in range(args.steps):
+        with ops.on("main"):
+            ev[0].record()
+        gp.build_gram()
+        with ops.on("main"):
+            ev[1].record()
+        info = gp.factor()
+        with ops.on("main"):
+            ev[2].record()
+        alpha = gp.solve(Yd) if info == 0 else None
+        with ops.on("main"):
+            ev[3].record()
+        torch.cuda.synchronize()
+        tsum += np.array([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]),
+                          ev[0].elapsed_time(ev[3])])
+    env["barrier"]()
+    clocks = sampler.stop()
+    launches = ops.h.launch_count() + ops.hp.launch_count() - l0
+    t = torch.tensor(tsum, dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    gram_ms, factor_ms, solve_ms, total_ms = (float(v) / args.steps for v in t.tolist())
+    stats = dict(gp.stats)
+    # end to end: host X, Y in, host alpha out (pageable), every step
+    e2e_steps = min(args.steps, 2)
+    alpha_host = None
+    env["barrier"]()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ops.set_samples(X, C3_SIGMA)
+        gp.build_gram()
+        if gp.factor() == 0:
+            alpha_host = gp.solve(Y).cpu().numpy()
+    torch.cuda.synchronize()
+    e2e_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3) / e2e_steps
+    resid = None
+    if info == 0 and rank == 0 and not args.skip_checks:
+        resid = residual_rows(C3_KERNEL, X, Y, alpha_host if alpha_host is not None else alpha.cpu().numpy(), C3_SIGMA, nrows=96)
+    total_launches = int(env["sum_over_ranks"](launches))
+    flops = learn_flops(N, M)
+    chol_tf = N ** 3 / 3.0 / factor_ms * 1e-9
+    line = {
+        "metric": "gp_learn_fp64_tflops", "value": flops / total_ms * 1e-9, "unit": "TFLOP/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {
+            "workload": "C5: GP Learn (Gram + Cholesky + solve) of ONE N=131072 model over all GPUs, "
+                        "Sum(Sum(Gaussian,Periodic),White), d=8, M=1, fp64",
+            "N": N, "d": C3_D, "M": M, "nb": nb, "grid": "%dx%d" % grid,
+            "layout": "2-D block-cyclic %d x %d, lower triangle only, %.1f GB per GPU" % (grid[0], grid[1], 4.0 * N * N / world * 1e-9),
+            "parallelism": "Pr x Pc block-cyclic Cholesky, NCCL broadcasts on row / column communicators, one-panel look-ahead",
+            "useful_flops": flops, "l2": "inputs larger than L2 (%.0f GB per GPU)" % (4.0 * N * N / world * 1e-9),
+            "learn_s": total_ms * 1e-3, "gram_s": gram_ms * 1e-3, "cholesky_s": factor_ms * 1e-3, "solve_s": solve_ms * 1e-3,
+            "cholesky_tflops_total": chol_tf, "cholesky_frac_of_peak": chol_tf / (FP64_PEAK_TFLOPS * world),
+            "bcast_GB_per_rank": stats["bcast_bytes"] * 1e-9 / max(1, args.steps + e2e_steps + 1),
+            "collectives_per_learn": stats["collectives"] / max(1, args.steps + e2e_steps + 1),
+            "info": info, "logdet": gp.logdet, "rel_residual_rows": resid,
+            "residual_note": "96 sampled rows, kernel rows evaluated by the CPU oracle",
+            "warmup_note": "DEVELOPMENT RUN: 1 full-size warm-up pass only" if args.large_quick_warmup
+                           else "%d full-size warm-up passes" % args.warmup,
+        },
+        "clocks": clocks,
+        "e2e": {"value": flops / e2e_ms * 1e-9, "unit": "TFLOP/s", "h2d_bytes_per_step": int(8 * N * (C3_D + M)) * world,
+                "d2h_bytes_per_step": int(8 * N * M) * world, "ms_per_step": e2e_ms, "steps": e2e_steps,
+                "host_buffers": "pageable numpy arrays, every rank uploads X and Y and downloads alpha"},
+        "gpu_launches": total_launches,
+        "roofline": {
+            "kernel": "dgemm_kernel (block-column trailing updates of the block-cyclic Cholesky, DMMA.8x8x4) per GPU",
+            "bound": "tensor", "achieved": chol_tf / world, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
+            "frac": chol_tf / world / FP64_PEAK_TFLOPS, "traffic": None,
+            "note": "achieved = N^3/3 / cholesky_s / n_gpus: the whole factorisation per GPU, panel chain, broadcasts "
+                    "and load imbalance included (not a single-kernel figure)",
+            "peak_source": "37.1 = measured DMMA issue rate (profiles/r01_fp64_probe.txt)",
+        },
+    }
+    ops.close()
+    del gp, Yd
+    torch.cuda.empty_cache()
+    return line
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of the trailing-update launch captured with ncu --set full
@@ -378,17 +536,81 @@ def run_gpu(args):
 TRAFFIC_TB_BYTES_PER_LAUNCH = 7.608593e9 + 3.756411e9
 
 
-def residual_check(torch, gpr_b200, h, Xd, Yd, N, dev):
-    """||(K + sigma^2 I) alpha - y|| / ||y|| at full size, K regenerated by the Gram kernel in row blocks."""
-    alpha = torch.from_numpy(h.alpha()).to(dev)
-    ldk = (N + 15) // 16 * 16
-    K = torch.empty(N, ldk, dtype=torch.float64, device=dev)
-    h._ck(h.lib.gprb200_gram_dev(h.h, K.data_ptr(), ldk, 1))
-    h.synchronize()
-    r = K[:, :N] @ alpha - Yd
-    out = float(torch.linalg.norm(r) / torch.linalg.norm(Yd))
-    del K
-    return {"rel_residual_alpha": out, "note": "||(K+s^2 I) alpha - y|| / ||y|| at N=%d (cond <= N+1)" % N}
+def run_predict_ci(args, env, N=16384, d=8, T=4096):
+    """Section 8(e) row 3 and the loop body of apps/GaussianProcessPredict.cpp:185-193: Predict + GetCredibleInterval.
+    Test points are independent: T / g per GPU, L replicated, no data-path collective. Reports batched points/s over
+    all ranks and the latency of ONE point per call (mean + interval), both through the host-pointer C-ABI."""
+    torch, gpr_b200 = env["torch"], env["gpr_b200"]
+    rank, local_rank, world = env["rank"], env["local_rank"], env["world"]
+    from gpr_b200 import dist as gd
+    rng = np.random.default_rng(SEED + 16)
+    X = rng.uniform(-1, 1, (N, d))
+    Y = np.sin(3.0 * X[:, :1]) + 0.1 * rng.standard_normal((N, 1))
+    Xs = rng.uniform(-1, 1, (T, d))
+    h = gpr_b200.Handle(local_rank)
+    ops, params = gpr_b200.KernelFactory.GetKernel(C3_KERNEL).lower()
+    h.set_kernel(ops, params)
+    g = gd.ShardedOutputsGP(h)
+    g.set_train(X, Y, C3_SIGMA)
+    g.learn()
+    b, e = gd.column_shard(T, rank, world)
+    g.credible_interval(Xs[:64], gather=False)
+    env["barrier"]()
+    t0 = time.perf_counter()
+    mean = h.predict(Xs[b:e])
+    ci = g.credible_interval(Xs, gather=False)
+    torch.cuda.synchronize()
+    batch_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3)
+    for i in range(3):
+        h.predict(Xs[i:i + 1], want_ci=True)
+    t0 = time.perf_counter()
+    reps = 20
+    for i in range(reps):
+        h.predict(Xs[i:i + 1], want_ci=True)
+    one_ms = (time.perf_counter() - t0) * 1e3 / reps
+    h.close()
+    return {"N": N, "d": d, "T": T, "points_per_s": T / batch_ms * 1e3, "batch_ms": batch_ms, "ms_per_point_t1": one_ms,
+            "sharding": "test points T / %d per GPU, L replicated, no collective" % world,
+            "finite": bool(np.isfinite(ci).all() and np.isfinite(mean).all())}
+
+
+def run_sharded_loglik(args, env, N=16384, iters=2):
+    """Section 8(e) row 4 at BASELINE config C4 (N = 16384, RationalQuadratic, P = 3): one log-likelihood + gradient
+    iteration with the inverse and the dK contraction sharded by row blocks over the ranks (gpr_b200.dist.ShardedLikelihood;
+    collective: all_gather of inv(L) column blocks + all_reduce of P doubles), against the single-GPU gprb200_loglik."""
+    torch, gpr_b200 = env["torch"], env["gpr_b200"]
+    rank, local_rank, world = env["rank"], env["local_rank"], env["world"]
+    from gpr_b200 import dist as gd
+    rng = np.random.default_rng(SEED + 4)
+    X = rng.uniform(-1, 1, (N, C3_D))
+    Y = np.sin(3.0 * X[:, :1]) + 0.1 * rng.standard_normal((N, 1))
+    ops, params = gpr_b200.KernelFactory.GetKernel("RationalQuadraticKernel(1,1.5,2,)").lower()
+    lo = gd.DeviceLikOps(local_rank, ops, params, X, Y, 1.0)
+    sl = gd.ShardedLikelihood(lo, block=512)
+    p = np.asarray(params)
+    sl.value_and_gradient(p, mode=1)
+    env["barrier"]()
+    t0 = time.perf_counter()
+    for it in range(iters):
+        v, g = sl.value_and_gradient(p * (1.0 + 0.01 * (it + 1)), mode=1)
+    torch.cuda.synchronize()
+    ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3) / iters
+    one = None
+    if rank == 0:
+        h = lo.h
+        h.set_kernel_params(p * (1.0 + 0.01 * iters))
+        h.loglik(1, True, True, False)
+        t0 = time.perf_counter()
+        v1, g1, _ = h.loglik(1, True, True, False)
+        torch.cuda.synchronize()
+        one = {"ms": (time.perf_counter() - t0) * 1e3, "grad": [float(x) for x in g1]}
+    lo.close()
+    if rank != 0:
+        return None
+    return {"N": N, "P": 3, "n_gpus": world, "iteration_ms": ms, "single_gpu_iteration_ms": one["ms"],
+            "collective": "all_gather of inv(L) column blocks (%.2f GB per iteration) + all_reduce of P doubles"
+                          % (sl.stats["gathered_bytes"] / (iters + 1) * 1e-9),
+            "grad": [float(x) for x in g], "grad_vs_1gpu": float(np.max(np.abs(g - np.array(one["grad"]))) / np.max(np.abs(g)))}
 
 
 def run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier, max_over_ranks):
@@ -729,61 +951,6 @@ def run_sparse(torch, gpr_b200, local_rank, n=262144, m=4096, d=8):
             "variance_min": float(var.min())}
 
 
-def run_block_cyclic(args, torch, gpr_b200, rank, local_rank, world, dev, dist):
-    """C5: ONE model of N = 131072 samples factored across all ranks (block-cyclic Cholesky, NCCL panel broadcasts,
-    gpr_b200/dist.py) + distributed solve. Strong scaling of a single large problem; device-timed, max over ranks."""
-    from gpr_b200 import dist as gd
-    N, nb = args.large_n, args.large_nb
-    rng = np.random.default_rng(SEED + 131)
-    X = rng.uniform(-1, 1, (N, C3_D))
-    Y = (np.sin(3.0 * X[:, :1]) + 0.5 * np.cos(2.0 * X[:, 1:2] + X[:, 2:3]) + 0.1 * rng.standard_normal((N, 1)))
-    ops_, params = gpr_b200.KernelFactory.GetKernel(C3_KERNEL).lower()
-    ops = gd.DeviceOps(local_rank, ops_, params, X, C3_SIGMA)
-    # warm-up on a small problem with the same code path (NCCL communicator, allocator, kernel attributes)
-    warm = gd.BlockCyclicGP(ops, 8192, nb=nb)
-    warm.learn(Y[:8192])
-    del warm
-    torch.cuda.empty_cache()
-    gp = gd.BlockCyclicGP(ops, N, nb=nb)
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-    dist.barrier()
-    torch.cuda.synchronize()
-    with ops.on("main"):
-        ev[0].record()
-    gp.build_gram()
-    with ops.on("main"):
-        ev[1].record()
-    info = gp.factor()
-    with ops.on("main"):
-        ev[2].record()
-    alpha = gp.solve(Y) if info == 0 else None
-    with ops.on("main"):
-        ev[3].record()
-    torch.cuda.synchronize()
-    t = torch.tensor([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]),
-                      ev[0].elapsed_time(ev[3])], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    gram_ms, factor_ms, solve_ms, total_ms = (float(v) for v in t.tolist())
-    # residual on a sample of rows: ||(K + s^2 I) alpha - y|| over 512 rows, K rows regenerated by the Gram kernel
-    resid = None
-    if info == 0 and rank == 0:
-        rows = 512
-        Kr = ops.empty(rows, N)
-        with ops.on("main"):
-            ops.gram_block(N - rows, 0, Kr)
-            r = Kr @ alpha - ops.from_host(Y[N - rows:])
-            resid = float(torch.linalg.norm(r) / np.linalg.norm(Y[N - rows:]))
-    out = {"metric": "gp_learn_large_n_s", "N": N, "nb": nb, "n_gpus": world, "info": info,
-           "learn_s": total_ms * 1e-3, "gram_s": gram_ms * 1e-3, "cholesky_s": factor_ms * 1e-3, "solve_s": solve_ms * 1e-3,
-           "cholesky_tflops_total": N ** 3 / 3.0 / factor_ms * 1e-9,
-           "cholesky_frac_of_peak": N ** 3 / 3.0 / factor_ms * 1e-9 / (FP64_PEAK_TFLOPS * world),
-           "scaling": "strong (one N x N problem over all ranks)", "logdet": gp.logdet,
-           "bcast_GB_per_rank": gp.stats["bcast_bytes"] * 1e-9, "rel_residual_rows": resid,
-           "layout": "block-cyclic over a 1 x %d grid, lower triangle only, %.1f GB per GPU" % (world, 4.0 * N * N / world * 1e-9)}
-    ops.close()
-    return out
-
-
 def run_cpu_baseline():
     """The reference's own CPU code (oracle/_ref) on a bounded sample of the same workload, all host threads."""
     try:
@@ -823,6 +990,11 @@ def main():
     ap.add_argument("--skip-hostio", action="store_true")
     ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--large-nb", type=int, default=1024, help="block-column width of the block-cyclic Cholesky")
+    ap.add_argument("--grid", default="", help="PrxPc process grid of the block-cyclic Cholesky (default: dist.default_grid)")
+    ap.add_argument("--large-quick-warmup", action="store_true",
+                    help="development only: ONE full-size warm-up pass at N > 1 GPUs instead of --warmup of them")
+    ap.add_argument("--skip-replicas", action="store_true")
+    ap.add_argument("--skip-predict-ci", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")
     args = ap.parse_args()

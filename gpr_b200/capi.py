@@ -37,6 +37,8 @@ _PROTOS = {
     "gprb200_solve_alpha": (C.c_int, [C.c_void_p]),
     "gprb200_get_alpha": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_alpha_dev": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
+    "gprb200_get_factor_dev": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_void_p)]),
+    "gprb200_dgram_contract_rows_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_get_core": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_factor": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_logdet": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
@@ -262,6 +264,18 @@ class Handle:
         ld = C.c_int64()
         self._ck(self.lib.gprb200_get_alpha_dev(self.h, C.byref(p), C.byref(ld)))
         return p.value, ld.value
+
+    def factor_dev(self):
+        """(device pointer of L, leading dimension, device pointer of the inverted 128 x 128 diagonal blocks)"""
+        p, q = C.c_void_p(), C.c_void_p()
+        ld = C.c_int64()
+        self._ck(self.lib.gprb200_get_factor_dev(self.h, C.byref(p), C.byref(ld), C.byref(q)))
+        return p.value, ld.value, q.value
+
+    def dgram_contract_rows_dev(self, row0, nrows, dS_ptr, lds):
+        out = np.empty(self.P)
+        self._ck(self.lib.gprb200_dgram_contract_rows_dev(self.h, int(row0), int(nrows), C.c_void_p(dS_ptr), int(lds), _ptr(out)))
+        return out
 
     def core(self):
         Cm = np.empty((self.N, self.N))

@@ -732,6 +732,27 @@ int gprb200_get_alpha_dev(gprb200_handle h, const double** d_alpha, int64_t* ld)
     return 0;
 }
 
+int gprb200_get_factor_dev(gprb200_handle h, const double** d_L, int64_t* ld, const double** d_invL) {
+    if (!h || !d_L || !ld) return -2;
+    GP_TRY(use_device(h));
+    GP_TRY(ensure_factor(h));
+    *d_L = h->dL;
+    *ld = h->ldk;
+    if (d_invL) *d_invL = h->dInvL;
+    return 0;
+}
+
+int gprb200_dgram_contract_rows_dev(gprb200_handle h, int64_t row0, int64_t nrows, const double* dS, int64_t lds,
+                                    double* out) {
+    if (!h || !dS || !out) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, c->have_train && c->have_kernel, "dgram_contract_rows: need samples and a kernel"));
+    GP_TRY(require(c, row0 >= 0 && nrows > 0 && row0 + nrows <= c->N && lds >= c->N,
+                   "dgram_contract_rows: rows outside the training set or lds < N"));
+    return dgram_contract_xy(c, c->dX + row0 * c->d, nrows, c->dX, c->N, dS, lds, out);
+}
+
 int gprb200_get_core(gprb200_handle h, double* C) {
     if (!h || !C) return -2;
     Ctx* c = h;

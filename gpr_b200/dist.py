@@ -553,6 +553,26 @@ class ShardedOutputsGP:
     def learn(self):
         self.h.learn(0)
 
+    def credible_interval(self, Xs, gather=True):
+        """GetCredibleInterval (lib/GaussianProcess.cpp:103-114; called once per test point by
+        apps/GaussianProcessPredict.cpp:185-193) for T test points: the points are independent, so rank r evaluates
+        the slice column_shard(T, r, g) against its own replica of L (K is small and factored on every rank). No
+        data-path collective; gather=True all_gathers the T scalars so every rank returns all of them."""
+        Xs = np.ascontiguousarray(np.atleast_2d(Xs), dtype=np.float64)
+        T = Xs.shape[0]
+        b, e = column_shard(T, self.rank, self.world)
+        local = self.h.credible_interval(Xs[b:e]) if e > b else np.empty(0)
+        if not gather or self.world == 1:
+            return local
+        cuts = [column_shard(T, r, self.world) for r in range(self.world)]
+        wmax = max(hi - lo for lo, hi in cuts)
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(self.group) == "nccl" else torch.device("cpu")
+        pad = torch.zeros(wmax, dtype=torch.float64, device=dev)
+        pad[:e - b] = torch.as_tensor(local).to(dev)
+        parts = [torch.empty_like(pad) for _ in range(self.world)]
+        dist.all_gather(parts, pad, group=self.group)
+        return torch.cat([p[:hi - lo] for p, (lo, hi) in zip(parts, cuts)]).cpu().numpy()
+
     def predict(self, Xs, gather=False):
         """Mean of this rank's output columns for the test points Xs (T x d); gather=True returns T x M on every rank."""
         mean = self.h.predict(Xs)
@@ -567,3 +587,147 @@ class ShardedOutputsGP:
         parts = [torch.empty_like(pad) for _ in range(self.world)]
         dist.all_gather(parts, pad, group=self.group)
         return torch.cat([p[:, :e - b] for p, (b, e) in zip(parts, widths)], dim=1).cpu().numpy()
+
+
+class _DeviceView:
+    """zero-copy torch view of a device buffer owned by the library (CUDA array interface)"""
+
+    def __init__(self, ptr, shape, strides=None):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f8", "data": (int(ptr), False), "version": 2,
+                                         "strides": strides}
+
+
+class DeviceLikOps:
+    """Local operations of ShardedLikelihood on one GPU: a C-ABI handle that holds the replicated model (samples,
+    labels, factor) and the device building blocks (triangular solve, FP64 tensor-core GEMM, fused dK contraction)."""
+
+    def __init__(self, device_index, ops, params, X, Y, sigma):
+        from .capi import Handle
+        self.device = torch.device("cuda", device_index)
+        torch.cuda.set_device(self.device)
+        self.h = Handle(device_index)
+        self.h.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        self.h.set_kernel(ops, params)
+        self.h.set_train(X, Y, sigma)
+        self.N, self.M, self.P = self.h.N, self.h.M, self.h.P
+        self._L = self._invL = self._alpha = None
+
+    def refactor(self, params, mode):
+        """New kernel parameters -> Gram + Cholesky + alpha on THIS rank (replicated); returns the M likelihood values."""
+        self.h.set_kernel_params(params)
+        value = self.h.loglik(mode, True, False, False)[0]
+        lp, ld, ip = self.h.factor_dev()
+        self._L = torch.as_tensor(_DeviceView(lp, (self.N, ld)), device=self.device)
+        self._invL = ip
+        ap, lda = self.h.alpha_dev()
+        self._alpha = torch.as_tensor(_DeviceView(ap, (self.N, lda)), device=self.device)
+        return value
+
+    def alpha(self):
+        return self._alpha[:, :self.M]
+
+    def zeros(self, rows, cols):
+        return torch.zeros((rows, cols), dtype=torch.float64, device=self.device)
+
+    def trtri_panel(self, o, w, out):
+        """out ((N - o) x w, zeroed with the identity on top by the caller) <- L[o:, o:]^-1 out: columns o..o+w of
+        W = inv(L), rows o..N (everything above is zero)."""
+        h, L = self.h, self._L
+        n = self.N - o
+        h._ck(h.lib.gprb200_trsm_dev(h.h, L.data_ptr() + 8 * (o * L.stride(0) + o), L.stride(0),
+                                     self._invL + 8 * (o // 128) * 128 * 128, n, out.data_ptr(), out.stride(0), w, 0))
+
+    def atb(self, A, B, out):
+        """out = A^T B on the FP64 tensor path (A: K x m, B: K x n)."""
+        h = self.h
+        h._ck(h.lib.gprb200_gemm_dev(h.h, 2, out.shape[0], out.shape[1], A.shape[0], ctypes.c_double(1.0), A.data_ptr(),
+                                     A.stride(0), B.data_ptr(), B.stride(0), ctypes.c_double(0.0), out.data_ptr(),
+                                     out.stride(0), 0))
+
+    def outer_minus(self, o, m, S):
+        """S (m x N) <- alpha[o:o+m] alpha^T - S, summed over the output columns (C is subtracted ONCE,
+        include/Likelihood.h:280-282)."""
+        h, a = self.h, self._alpha
+        h._ck(h.lib.gprb200_gemm_dev(h.h, 0, m, self.N, self.M, ctypes.c_double(1.0), a.data_ptr() + 8 * o * a.stride(0),
+                                     a.stride(0), a.data_ptr(), a.stride(0), ctypes.c_double(-1.0), S.data_ptr(), S.stride(0), 0))
+
+    def contract_rows(self, o, m, S):
+        return self.h.dgram_contract_rows_dev(o, m, S.data_ptr(), S.stride(0))
+
+    def close(self):
+        self.h.close()
+
+
+class ShardedLikelihood:
+    """GaussianLogLikelihood value and parameter gradient (include/Likelihood.h:231-285) over g GPUs for a model whose
+    factor fits one GPU (N <= 32768; BASELINE config C4 is N = 16384).
+
+    The gradient 1/2 tr((alpha alpha^T - C) dK_p) reads ALL of C = (K + sigma^2 I)^-1; forming C from the factor is
+    2/3 of the iteration on one GPU (TRTRI + LAUUM, 2 N^3 / 3 flop). Here the factor is replicated (every rank factors
+    K itself: N^3 / 3, cheaper than shipping L) and the inverse and the contraction are sharded by ROW BLOCKS of
+    A = alpha alpha^T - C, block i (width m) on rank i mod g:
+        1. W = inv(L): each rank solves L W_j = E_j for its column blocks j (rows above o_j are zero)      N^3 / (3 g)
+        2. all_gather of the column blocks (one round per g blocks, NVLink)                                4 N^2 bytes
+        3. C[R_i, :] = W[:, R_i]^T W, one tensor-core GEMM per block pair, k >= max(o_i, o_j)             2 N^3 / (3 g)
+        4. A[R_i, :] = alpha[R_i] alpha^T - C[R_i, :], fused contraction with dK_p(x_i, x_j) generated on the fly
+        5. all_reduce of the P partial sums.
+    No rank ever holds all of C. ops: DeviceLikOps, or the numpy stand-in of the CPU tests."""
+
+    def __init__(self, ops, block=512, group=None):
+        self.ops = ops
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if block % 128 != 0:
+            raise ValueError("ShardedLikelihood: block must be a multiple of 128")
+        self.m = int(block)
+        N = ops.N
+        self.nblk = (N + self.m - 1) // self.m
+        self.width = [min(self.m, N - j * self.m) for j in range(self.nblk)]
+        self.mine = list(range(self.rank, self.nblk, self.world))
+        self.stats = {"gathered_bytes": 0}
+
+    def value_and_gradient(self, params, mode=1):
+        """Returns (value[M], grad[P]), identical on every rank."""
+        ops, m, N, g = self.ops, self.m, self.ops.N, self.world
+        value = ops.refactor(params, mode)
+        rounds = (self.nblk + g - 1) // g
+        Wall = {}
+        for t in range(rounds):
+            base = t * g * m                     # first row that can be non-zero in this round's panels
+            j = t * g + self.rank
+            send = ops.zeros(N - base, m)
+            if j < self.nblk:
+                o, w = j * m, self.width[j]
+                top = send[o - base:]
+                top[:w, :w].copy_(torch.eye(w, dtype=torch.float64, device=top.device))
+                ops.trtri_panel(o, w, top)
+            if g > 1:
+                parts = [torch.empty_like(send) for _ in range(g)]
+                dist.all_gather(parts, send, group=self.group)
+                self.stats["gathered_bytes"] += send.numel() * 8 * g
+            else:
+                parts = [send]
+            for r2 in range(g):
+                if t * g + r2 < self.nblk:
+                    Wall[t * g + r2] = (parts[r2], base)
+        part = np.zeros(ops.P)
+        lds = (N + 1) // 2 * 2
+        for i in self.mine:
+            oi, wi = i * m, self.width[i]
+            Wi, bi = Wall[i]
+            S = ops.zeros(wi, lds)
+            for j in range(self.nblk):
+                oj, wj = j * m, self.width[j]
+                Wj, bj = Wall[j]
+                k0 = max(oi, oj)
+                ops.atb(Wi[k0 - bi:, :wi], Wj[k0 - bj:, :wj], S[:, oj:oj + wj])
+            ops.outer_minus(oi, wi, S)
+            part += ops.contract_rows(oi, wi, S)
+        t = torch.as_tensor(part)
+        if g > 1:
+            dev = getattr(ops, "device", torch.device("cpu"))
+            t = t.to(dev)
+            dist.all_reduce(t, group=self.group)
+            t = t.cpu()
+        return value, 0.5 * t.numpy()

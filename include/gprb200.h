@@ -136,6 +136,10 @@ int gprb200_solve_alpha(gprb200_handle h);      /* alpha from the current factor
 
 int gprb200_get_alpha(gprb200_handle h, double* alpha /* N x M */);
 int gprb200_get_alpha_dev(gprb200_handle h, const double** d_alpha, int64_t* ld);
+/* Device view of the factor held by the handle: L (N x N, ld, lower; the strict upper part is stale K) and, if d_invL is
+ * not NULL, the ceil(N/128) inverted 128 x 128 diagonal blocks gprb200_trsm_dev takes. Valid until the next call that
+ * re-factorises. Lets a multi-GPU driver share the solve / inverse work of one replicated factor (dist.py). */
+int gprb200_get_factor_dev(gprb200_handle h, const double** d_L, int64_t* ld, const double** d_invL);
 /* C = inv(K + sigma^2 I), formed lazily from the factor (InvertKernelMatrix, lib/GaussianProcess.cpp:531-618) */
 int gprb200_get_core(gprb200_handle h, double* C /* N x N */);
 /* lower Cholesky factor L (row-major, strictly-upper part zeroed) */
@@ -221,6 +225,12 @@ int gprb200_dgram(gprb200_handle h, double* D_out);
  *   grad[p]  = 0.5 tr((alpha alpha^T - C) dK/dtheta_p)           (P values; may be NULL)  (:280-282)
  *   jac[i,p] = 0.5 tr((alpha_i alpha_i^T - C) dK/dtheta_p)       (M x P;   may be NULL)  (:335-341) */
 int gprb200_loglik(gprb200_handle h, int mode, double* value, double* grad, double* jac);
+/* Row-block share of the likelihood-gradient contraction (include/Likelihood.h:268-282 computes P full N x N products
+ * for these traces): out[p] = sum_{i < nrows, j < N} dS[i * lds + j] * dK_p(x_{row0+i}, x_j), dS a DEVICE nrows x N
+ * block of a symmetric weight matrix (e.g. rows of alpha alpha^T - C), dK generated on the fly, out P HOST doubles.
+ * Summing the results of disjoint row blocks over ranks (ncclAllReduce of P doubles) gives tr(S dK_p). */
+int gprb200_dgram_contract_rows_dev(gprb200_handle h, int64_t row0, int64_t nrows, const double* dS, int64_t lds,
+                                    double* out);
 /* q[k] = y_k^T (K + sigma^2 I)^-1 y_k, the data-fit term of include/Likelihood.h:175 (M values) */
 int gprb200_quadform(gprb200_handle h, double* q);
 

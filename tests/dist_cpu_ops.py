@@ -103,3 +103,47 @@ class CpuOps:
 
     def close(self):
         pass
+
+
+class CpuLikOps:
+    """numpy stand-in for gpr_b200.dist.DeviceLikOps (ShardedLikelihood's local operations)."""
+    device = torch.device("cpu")
+
+    def __init__(self, kernel_string, X, Y, sigma):
+        self.k0 = orc.parse_kernel(kernel_string)
+        self.X = np.ascontiguousarray(X, dtype=np.float64)
+        self.Y = np.ascontiguousarray(Y, dtype=np.float64)
+        self.sigma = float(sigma)
+        self.N, self.M = self.Y.shape
+        self.P = orc.num_params(self.k0)
+
+    def refactor(self, params, mode):
+        self.k = orc.set_params(self.k0, list(params))
+        K = orc.kernel_matrix(self.k, self.X, self.X) + self.sigma ** 2 * np.eye(self.N)
+        self.L = np.linalg.cholesky(K)
+        self.a = sla.cho_solve((self.L, True), self.Y)
+        logdet = 2.0 * np.sum(np.log(np.diag(self.L)))
+        q = np.sum(self.Y * self.a, axis=0)
+        return -0.5 * q - 0.5 * logdet - 0.5 * self.N * np.log(2 * np.pi)
+
+    def alpha(self):
+        return torch.as_tensor(self.a)
+
+    def zeros(self, rows, cols):
+        return torch.zeros((rows, cols), dtype=torch.float64)
+
+    def trtri_panel(self, o, w, out):
+        out.copy_(torch.as_tensor(sla.solve_triangular(self.L[o:, o:], out.numpy(), lower=True)))
+
+    def atb(self, A, B, out):
+        out.copy_(torch.as_tensor(A.numpy().T @ B.numpy()))
+
+    def outer_minus(self, o, m, S):
+        S[:, :self.N] = torch.as_tensor(self.a[o:o + m] @ self.a.T) - S[:, :self.N]
+
+    def contract_rows(self, o, m, S):
+        D = orc.kernel_derivative(self.k, self.X[o:o + m], self.X)      # (P, m, N)
+        return np.einsum("pij,ij->p", D, S.numpy()[:, :self.N])
+
+    def close(self):
+        pass

@@ -50,3 +50,49 @@ def test_sharded_outputs_single_rank_is_the_plain_model():
     assert g.shard == (0, 37)
     assert np.array_equal(g.predict(Xs, gather=True), h.predict(Xs))
     h.close()
+
+
+@pytest.mark.parametrize("N,block,M,kname", [(700, 128, 2, "rq"), (1500, 512, 1, "sum3"), (1111, 256, 3, "general13")])
+def test_sharded_likelihood_device_ops_match_oracle_and_single_gpu(N, block, M, kname):
+    """ShardedLikelihood on one rank (same code path as g ranks, no process group) against the oracle's
+    GaussianLogLikelihood gradient (include/Likelihood.h:231-285) and against gprb200_loglik."""
+    import gpr_b200
+    from gpr_b200 import dist as gd
+    from oracle import gpr_oracle as orc
+    X, Y = make_problem(N, 4, M, seed=8)
+    ops_, params = gpr_b200.KernelFactory.GetKernel(KERNELS[kname]).lower()
+    lo = gd.DeviceLikOps(0, ops_, params, X, Y, 1.0)
+    sl = gd.ShardedLikelihood(lo, block=block)
+    p = np.array(params) * 1.03
+    v, g = sl.value_and_gradient(p, mode=gpr_b200.capi.LOGLIK_TRUE)
+    k = orc.set_params(orc.parse_kernel(KERNELS[kname]), list(p))
+    o = orc.OracleGP(k, X, Y, 1.0)
+    o.learn()
+    assert rel_err(g, o.loglik_grad()) <= 1e-8          # BASELINE.json tolerance on the likelihood gradient
+    assert rel_err(v, o.loglik_value(clamp=False)) <= 1e-8
+    h = gpr_b200.Handle(0)
+    h.set_kernel(ops_, list(p))
+    h.set_train(X, Y, 1.0)
+    v1, g1, _ = h.loglik(gpr_b200.capi.LOGLIK_TRUE, True, True, False)
+    assert rel_err(g, g1) <= 1e-10 and rel_err(v, v1) <= 1e-13
+    h.close()
+    lo.close()
+
+
+def test_sharded_credible_interval_single_rank_is_the_plain_call():
+    import gpr_b200
+    from gpr_b200 import dist as gd
+    X, Y = make_problem(600, 5, 4, seed=10)
+    ops_, params = gpr_b200.KernelFactory.GetKernel(KERNELS["sum3"]).lower()
+    h = gpr_b200.Handle(0)
+    h.set_kernel(ops_, params)
+    g = gd.ShardedOutputsGP(h)
+    g.set_train(X, Y, 1.0)
+    g.learn()
+    Xs = X[:9] + 0.02
+    assert np.array_equal(g.credible_interval(Xs), h.credible_interval(Xs))
+    from oracle import gpr_oracle as orc
+    o = orc.OracleGP(KERNELS["sum3"], X, Y, 1.0)
+    o.learn()
+    assert np.max(np.abs(g.credible_interval(Xs) - np.array([o.credible_interval(x) for x in Xs]))) <= 1e-8
+    h.close()
