@@ -215,6 +215,9 @@ def run_gpu(args):
                 line["config"]["replicas"] = {"what": "one independent C3 model per GPU, no collective (the round-1 headline)",
                                               "tflops_total": rep["value"], "ms_per_step": rep["ms_per_step"]}
     torch.cuda.empty_cache()
+    if rank == 0:
+        sys.stderr.write("bench headline: " + json.dumps(line) + "\n")
+        sys.stderr.flush()
 
     predict = None if args.skip_predict else run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier,
                                                          max_over_ranks)
@@ -557,17 +560,19 @@ def run_predict_ci(args, env, N=16384, d=8, T=4096):
     g.credible_interval(Xs[:64], gather=False)
     env["barrier"]()
     t0 = time.perf_counter()
-    mean = h.predict(Xs[b:e])
-    ci = g.credible_interval(Xs, gather=False)
+    mean = g.predict(Xs[b:e])                      # this rank's output columns (may be none when M < g)
+    ci = g.credible_interval(Xs, gather=False)     # this rank's test points
     torch.cuda.synchronize()
     batch_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3)
-    for i in range(3):
-        h.predict(Xs[i:i + 1], want_ci=True)
-    t0 = time.perf_counter()
-    reps = 20
-    for i in range(reps):
-        h.predict(Xs[i:i + 1], want_ci=True)
-    one_ms = (time.perf_counter() - t0) * 1e3 / reps
+    one_ms = None
+    if g.shard[1] > g.shard[0]:
+        for i in range(3):
+            h.predict(Xs[i:i + 1], want_ci=True)
+        t0 = time.perf_counter()
+        reps = 20
+        for i in range(reps):
+            h.predict(Xs[i:i + 1], want_ci=True)
+        one_ms = (time.perf_counter() - t0) * 1e3 / reps
     h.close()
     return {"N": N, "d": d, "T": T, "points_per_s": T / batch_ms * 1e3, "batch_ms": batch_ms, "ms_per_point_t1": one_ms,
             "sharding": "test points T / %d per GPU, L replicated, no collective" % world,

@@ -548,10 +548,14 @@ class ShardedOutputsGP:
             if Y.shape[1] != e - b:
                 raise ValueError("ShardedOutputsGP: slice has %d columns, rank %d owns %d" % (Y.shape[1], self.rank, e - b))
         self.shard = (b, e)
-        self.h.set_train(X, np.ascontiguousarray(Y), sigma)
+        # a rank may own no output column (M < g): it still holds the samples and factors K for its test points
+        self.h.set_train(X, np.ascontiguousarray(Y) if e > b else None, sigma)
 
     def learn(self):
-        self.h.learn(0)
+        if self.shard[1] > self.shard[0]:
+            self.h.learn(0)
+        else:
+            self.h.factorize()
 
     def credible_interval(self, Xs, gather=True):
         """GetCredibleInterval (lib/GaussianProcess.cpp:103-114; called once per test point by
@@ -575,7 +579,10 @@ class ShardedOutputsGP:
 
     def predict(self, Xs, gather=False):
         """Mean of this rank's output columns for the test points Xs (T x d); gather=True returns T x M on every rank."""
-        mean = self.h.predict(Xs)
+        if self.shard[1] > self.shard[0]:
+            mean = self.h.predict(Xs)
+        else:
+            mean = np.empty((np.atleast_2d(Xs).shape[0], 0))
         if not gather or self.world == 1:
             return mean
         t = torch.as_tensor(np.ascontiguousarray(mean))
