@@ -38,7 +38,7 @@ _PROTOS = {
     "gprb200_get_alpha": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_alpha_dev": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "gprb200_get_factor_dev": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_void_p)]),
-    "gprb200_dgram_contract_rows_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
+    "gprb200_dgram_contract_rows_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
     "gprb200_get_core": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_factor": (C.c_int, [C.c_void_p, C.c_void_p]),
     "gprb200_get_logdet": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
@@ -53,6 +53,8 @@ _PROTOS = {
                                                 C.c_void_p]),
     "gprb200_trsm_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                    C.c_int64, C.c_int]),
+    "gprb200_trtri_cols_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+                                         C.c_void_p, C.c_int64]),
     "gprb200_logdet_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_double)]),
     "gprb200_predict": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "gprb200_predict_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
@@ -272,9 +274,10 @@ class Handle:
         self._ck(self.lib.gprb200_get_factor_dev(self.h, C.byref(p), C.byref(ld), C.byref(q)))
         return p.value, ld.value, q.value
 
-    def dgram_contract_rows_dev(self, row0, nrows, dS_ptr, lds):
+    def dgram_contract_rows_dev(self, row0, nrows, ncols, dS_ptr, lds):
         out = np.empty(self.P)
-        self._ck(self.lib.gprb200_dgram_contract_rows_dev(self.h, int(row0), int(nrows), C.c_void_p(dS_ptr), int(lds), _ptr(out)))
+        self._ck(self.lib.gprb200_dgram_contract_rows_dev(self.h, int(row0), int(nrows), int(ncols), C.c_void_p(dS_ptr), int(lds),
+                                                          _ptr(out)))
         return out
 
     def core(self):

@@ -276,7 +276,7 @@ int quad_forms(Ctx* c, const double* dXa, const double* dXb, int64_t T, double* 
 int predict_impl(Ctx* c, const double* dXs, int64_t T, double* d_mean, int64_t ld_mean, double* d_ci) {
     GP_TRY(require(c, c->have_kernel, "predict: no kernel"));
     GP_TRY(require(c, c->have_train, "predict: gaussian process is not initialized"));
-    if (!c->have_alpha) GP_TRY(ensure_alpha(c));
+    if (d_mean && !c->have_alpha) GP_TRY(ensure_alpha(c));   // the credible interval alone needs only the factor
     const int64_t N = c->N, M = c->M;
     // Predict stays asynchronous (a per-frame call must not cost a host synchronisation): the phase time is taken
     // with two persistent events and resolved only when gprb200_phase_ms asks for it.
@@ -742,15 +742,15 @@ int gprb200_get_factor_dev(gprb200_handle h, const double** d_L, int64_t* ld, co
     return 0;
 }
 
-int gprb200_dgram_contract_rows_dev(gprb200_handle h, int64_t row0, int64_t nrows, const double* dS, int64_t lds,
-                                    double* out) {
+int gprb200_dgram_contract_rows_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_t ncols, const double* dS,
+                                    int64_t lds, double* out) {
     if (!h || !dS || !out) return -2;
     Ctx* c = h;
     GP_TRY(use_device(c));
     GP_TRY(require(c, c->have_train && c->have_kernel, "dgram_contract_rows: need samples and a kernel"));
-    GP_TRY(require(c, row0 >= 0 && nrows > 0 && row0 + nrows <= c->N && lds >= c->N,
-                   "dgram_contract_rows: rows outside the training set or lds < N"));
-    return dgram_contract_xy(c, c->dX + row0 * c->d, nrows, c->dX, c->N, dS, lds, out);
+    GP_TRY(require(c, row0 >= 0 && nrows > 0 && row0 + nrows <= c->N && ncols > 0 && ncols <= c->N && lds >= ncols,
+                   "dgram_contract_rows: rows / columns outside the training set or lds < ncols"));
+    return dgram_contract_xy(c, c->dX + row0 * c->d, nrows, c->dX, ncols, dS, lds, out);
 }
 
 int gprb200_get_core(gprb200_handle h, double* C) {
@@ -861,6 +861,16 @@ int gprb200_trsm_dev(gprb200_handle h, const double* dL, int64_t ldl, const doub
     Ctx* c = h;
     GP_TRY(use_device(c));
     return transposed ? trsm_lower_bwd(c, dL, ldl, dInvL, n, dB, ldb, M) : trsm_lower_fwd(c, dL, ldl, dInvL, n, dB, ldb, M);
+}
+
+int gprb200_trtri_cols_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, int64_t col_block,
+                           int64_t first, int64_t stride, double* dW, int64_t ldw) {
+    if (!h || !dL || !dInvL || !dW) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, n > 0 && col_block > 0 && col_block % NB == 0 && first >= 0 && stride > 0 && (ldw & 1) == 0 &&
+                          (ldl & 1) == 0, "trtri_cols: col_block must be a multiple of 128, leading dimensions even"));
+    return trtri_cols(c, dL, ldl, dInvL, n, col_block, first, stride, dW, ldw);
 }
 
 int gprb200_logdet_dev(gprb200_handle h, const double* dL, int64_t ld, int64_t n, double* logdet) {

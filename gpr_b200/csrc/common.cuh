@@ -161,6 +161,8 @@ int trsm_lower_fwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int
 int trsm_lower_bwd(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* B, int64_t ldb,
                    int64_t M);
 int inverse_from_factor(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, double* C, int64_t ldc);
+int trtri_cols(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, int64_t cb, int64_t first,
+               int64_t stride, double* W, int64_t ldw);
 // util kernels (util.cu)
 int copy2d(Ctx* c, double* dst, int64_t ldd, const double* src, int64_t lds, int64_t rows, int64_t cols);
 int fill2d(Ctx* c, double* dst, int64_t ldd, int64_t rows, int64_t cols, double v);

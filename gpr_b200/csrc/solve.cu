@@ -602,6 +602,63 @@ static int inverse_long_k(Ctx* c, const double* L, int64_t ldl, const double* in
     return rc;
 }
 
+// W = inv(L) restricted to the cyclic column blocks j = first, first + stride, ... (width cb, a multiple of NB) and
+// stored COMPACTLY: local column q * cb + t holds global column (first + q * stride) * cb + t. The columns of inv(L)
+// are independent, so g ranks that take first = rank, stride = g share the N^3 / 3 flop of the TRTRI with no exchange
+// (multi-GPU likelihood gradient, gpr_b200/dist.py: ShardedLikelihood). Same left-looking long-K sweep as the TRTRI half
+// of inverse_long_k; the local columns with a global index below a row r form a prefix of the compact matrix, so every
+// product is one GEMM on a contiguous column range. (The zero part above each column block is multiplied through:
+// the triangular k-skip of GemmArgs::ktri needs global column indices.)
+int trtri_cols(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, int64_t cb, int64_t first,
+               int64_t stride, double* W, int64_t ldw) {
+    const int64_t nblk = (N + cb - 1) / cb;
+    auto nloc = [&](int64_t x) {   // local columns whose global index is < x
+        int64_t cnt = 0;
+        for (int64_t j = first; j < nblk; j += stride) {
+            const int64_t o = j * cb, w = (N - o < cb) ? (N - o) : cb;
+            if (x <= o) break;
+            cnt += (x - o < w) ? (x - o) : w;
+        }
+        return cnt;
+    };
+    const int64_t ncl = nloc(N);
+    if (ncl <= 0) return 0;
+    GP_TRY(fill2d(c, W, ldw, N, ncl, 0.0));
+    constexpr int64_t WS = 512;
+    for (int64_t s0 = 0; s0 < N; s0 += WS) {
+        const int64_t ws = (N - s0 < WS) ? (N - s0) : WS;
+        const int64_t n0 = nloc(s0);
+        if (s0 > 0 && n0 > 0) {
+            GemmArgs t{};
+            t.A = L + s0 * ldl; t.lda = ldl; t.B = W; t.ldb = ldw; t.C = W + s0 * ldw; t.ldc = ldw;
+            t.M = (int)ws; t.N = (int)n0; t.K = (int)s0; t.alpha = 1.0; t.beta = 0.0;
+            GP_TRY(gemm(c, GEMM_NN, t));
+        }
+        for (int64_t r0 = s0; r0 < s0 + ws; r0 += NB) {
+            const int n = (int)((N - r0 < NB) ? (N - r0) : NB);
+            const double* invk = invL + (r0 / NB) * (int64_t)NB * NB;
+            double* Wr = W + r0 * ldw;
+            const int64_t nr = nloc(r0);
+            if (r0 > s0 && nr > 0) {  // X_r += L[r, s0:r0] W[s0:r0, :nr]
+                GemmArgs u{};
+                u.A = L + r0 * ldl + s0; u.lda = ldl; u.B = W + s0 * ldw; u.ldb = ldw; u.C = Wr; u.ldc = ldw;
+                u.M = n; u.N = (int)nr; u.K = (int)(r0 - s0); u.alpha = 1.0; u.beta = 1.0;   // columns new in this super-row hold zeros
+                GP_TRY(gemm(c, GEMM_NN, u));
+            }
+            if (r0 > 0 && nr > 0) {  // W[r, :nr] = -inv(L_rr) X_r, in place (one row tile: every CTA owns its columns)
+                GemmArgs d{};
+                d.A = invk; d.lda = NB; d.B = Wr; d.ldb = ldw; d.C = Wr; d.ldc = ldw;
+                d.M = n; d.N = (int)nr; d.K = n; d.alpha = -1.0; d.beta = 0.0;
+                GP_TRY(gemm(c, GEMM_NN, d));
+            }
+            const int64_t j = r0 / cb;   // the diagonal block inv(L_rr) itself, if this column block is a local one
+            if (j >= first && (j - first) % stride == 0)
+                GP_TRY(copy2d(c, Wr + nr, ldw, invk, NB, n, n));
+        }
+    }
+    return 0;
+}
+
 // K5: C = (L L^T)^-1 from the factor, 2 N^3 / 3 flop (LAPACK dpotri's count; the reference calls dgetri / dpotri,
 // include/LAPACKUtils.h:50, :65). Two structured sweeps over C = I:
 //   forward  W = L^-1 is lower triangular: at block row k only columns [0, k0 + n) can be non-zero, so both GEMMs

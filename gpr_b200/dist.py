@@ -31,6 +31,7 @@ inject a numpy stand-in to run the same schedule under gloo with world_size 2, 3
 """
 import bisect
 import ctypes
+import time
 
 import numpy as np
 import torch
@@ -636,13 +637,13 @@ class DeviceLikOps:
     def zeros(self, rows, cols):
         return torch.zeros((rows, cols), dtype=torch.float64, device=self.device)
 
-    def trtri_panel(self, o, w, out):
-        """out ((N - o) x w, zeroed with the identity on top by the caller) <- L[o:, o:]^-1 out: columns o..o+w of
-        W = inv(L), rows o..N (everything above is zero)."""
+    def trtri_cols(self, first, stride, cb, ncl):
+        """Columns of W = inv(L) for the cyclic column blocks first, first + stride, ... (width cb), compact: N x ncl."""
         h, L = self.h, self._L
-        n = self.N - o
-        h._ck(h.lib.gprb200_trsm_dev(h.h, L.data_ptr() + 8 * (o * L.stride(0) + o), L.stride(0),
-                                     self._invL + 8 * (o // 128) * 128 * 128, n, out.data_ptr(), out.stride(0), w, 0))
+        W = torch.zeros((self.N, ncl), dtype=torch.float64, device=self.device)
+        h._ck(h.lib.gprb200_trtri_cols_dev(h.h, L.data_ptr(), L.stride(0), self._invL, self.N, cb, first, stride,
+                                           W.data_ptr(), W.stride(0)))
+        return W
 
     def atb(self, A, B, out):
         """out = A^T B on the FP64 tensor path (A: K x m, B: K x n)."""
@@ -651,15 +652,16 @@ class DeviceLikOps:
                                      A.stride(0), B.data_ptr(), B.stride(0), ctypes.c_double(0.0), out.data_ptr(),
                                      out.stride(0), 0))
 
-    def outer_minus(self, o, m, S):
-        """S (m x N) <- alpha[o:o+m] alpha^T - S, summed over the output columns (C is subtracted ONCE,
-        include/Likelihood.h:280-282)."""
+    def outer_minus(self, o, m, S, c0, c1, scale):
+        """S[:, c0:c1] <- scale (alpha[o:o+m] alpha[c0:c1]^T - S[:, c0:c1]), summed over the output columns (C is
+        subtracted ONCE, include/Likelihood.h:280-282)."""
         h, a = self.h, self._alpha
-        h._ck(h.lib.gprb200_gemm_dev(h.h, 0, m, self.N, self.M, ctypes.c_double(1.0), a.data_ptr() + 8 * o * a.stride(0),
-                                     a.stride(0), a.data_ptr(), a.stride(0), ctypes.c_double(-1.0), S.data_ptr(), S.stride(0), 0))
+        h._ck(h.lib.gprb200_gemm_dev(h.h, 0, m, c1 - c0, self.M, ctypes.c_double(scale), a.data_ptr() + 8 * o * a.stride(0),
+                                     a.stride(0), a.data_ptr() + 8 * c0 * a.stride(0), a.stride(0), ctypes.c_double(-scale),
+                                     S.data_ptr() + 8 * c0, S.stride(0), 0))
 
-    def contract_rows(self, o, m, S):
-        return self.h.dgram_contract_rows_dev(o, m, S.data_ptr(), S.stride(0))
+    def contract_rows(self, o, m, ncols, S):
+        return self.h.dgram_contract_rows_dev(o, m, ncols, S.data_ptr(), S.stride(0))
 
     def close(self):
         self.h.close()
@@ -673,10 +675,11 @@ class ShardedLikelihood:
     2/3 of the iteration on one GPU (TRTRI + LAUUM, 2 N^3 / 3 flop). Here the factor is replicated (every rank factors
     K itself: N^3 / 3, cheaper than shipping L) and the inverse and the contraction are sharded by ROW BLOCKS of
     A = alpha alpha^T - C, block i (width m) on rank i mod g:
-        1. W = inv(L): each rank solves L W_j = E_j for its column blocks j (rows above o_j are zero)      N^3 / (3 g)
-        2. all_gather of the column blocks (one round per g blocks, NVLink)                                4 N^2 bytes
-        3. C[R_i, :] = W[:, R_i]^T W, one tensor-core GEMM per block pair, k >= max(o_i, o_j)             2 N^3 / (3 g)
-        4. A[R_i, :] = alpha[R_i] alpha^T - C[R_i, :], fused contraction with dK_p(x_i, x_j) generated on the fly
+        1. W = inv(L): each rank inverts its own column blocks j (gprb200_trtri_cols_dev, long-K GEMMs)     ~2 N^3 / (3 g)
+        2. one all_gather of the compact column blocks (NVLink), one permuted copy into a row-major W     8 N^2 bytes
+        3. lower part of C[R_i, :] = W[o_i:, R_i]^T W[o_i:, :o_i + m], ONE tensor-core GEMM per row block     N^3 / (3 g)
+        4. A[R_i, :] = alpha[R_i] alpha^T - C[R_i, :] (strictly-lower blocks weighted twice: A is symmetric), fused
+           contraction with dK_p(x_i, x_j) generated on the fly
         5. all_reduce of the P partial sums.
     No rank ever holds all of C. ops: DeviceLikOps, or the numpy stand-in of the CPU tests."""
 
@@ -693,44 +696,46 @@ class ShardedLikelihood:
         self.width = [min(self.m, N - j * self.m) for j in range(self.nblk)]
         self.mine = list(range(self.rank, self.nblk, self.world))
         self.stats = {"gathered_bytes": 0}
+        self.profile = False        # True: synchronise after each phase and accumulate phase times in stats
+        self._W = None
 
     def value_and_gradient(self, params, mode=1):
         """Returns (value[M], grad[P]), identical on every rank."""
         ops, m, N, g = self.ops, self.m, self.ops.N, self.world
+        t0 = time.perf_counter()
         value = ops.refactor(params, mode)
-        rounds = (self.nblk + g - 1) // g
-        Wall = {}
-        for t in range(rounds):
-            base = t * g * m                     # first row that can be non-zero in this round's panels
-            j = t * g + self.rank
-            send = ops.zeros(N - base, m)
-            if j < self.nblk:
-                o, w = j * m, self.width[j]
-                top = send[o - base:]
-                top[:w, :w].copy_(torch.eye(w, dtype=torch.float64, device=top.device))
-                ops.trtri_panel(o, w, top)
-            if g > 1:
-                parts = [torch.empty_like(send) for _ in range(g)]
-                dist.all_gather(parts, send, group=self.group)
-                self.stats["gathered_bytes"] += send.numel() * 8 * g
-            else:
-                parts = [send]
-            for r2 in range(g):
-                if t * g + r2 < self.nblk:
-                    Wall[t * g + r2] = (parts[r2], base)
+        self._tick("factor", t0)
+        # 1 + 2: W = inv(L): every rank inverts its own cyclic column blocks (compact N x Q m), one all_gather, one
+        # permuted copy into the row-major N x (Q g m) matrix
+        t0 = time.perf_counter()
+        Q = (self.nblk + g - 1) // g
+        ncl = Q * m
+        Wloc = ops.trtri_cols(self.rank, g, m, ncl)
+        if g > 1:
+            Wg = torch.empty((g, N, ncl), dtype=torch.float64, device=Wloc.device)
+            dist.all_gather(list(Wg.unbind(0)), Wloc, group=self.group)
+            self.stats["gathered_bytes"] += Wg.numel() * 8
+        else:
+            Wg = Wloc.unsqueeze(0)
+        if self._W is None:
+            self._W = ops.zeros(N, Q * g * m)
+        W = self._W
+        W.view(N, Q, g, m).copy_(Wg.view(g, N, Q, m).permute(1, 2, 0, 3))
+        del Wg, Wloc
+        self._tick("trtri_gather", t0)
+        # 3 + 4: lower part of the owned row blocks of C = W^T W (S is symmetric: strictly-lower blocks count twice)
+        t0 = time.perf_counter()
         part = np.zeros(ops.P)
-        lds = (N + 1) // 2 * 2
         for i in self.mine:
             oi, wi = i * m, self.width[i]
-            Wi, bi = Wall[i]
-            S = ops.zeros(wi, lds)
-            for j in range(self.nblk):
-                oj, wj = j * m, self.width[j]
-                Wj, bj = Wall[j]
-                k0 = max(oi, oj)
-                ops.atb(Wi[k0 - bi:, :wi], Wj[k0 - bj:, :wj], S[:, oj:oj + wj])
-            ops.outer_minus(oi, wi, S)
-            part += ops.contract_rows(oi, wi, S)
+            nc = oi + wi
+            S = ops.zeros(wi, (nc + 1) // 2 * 2)
+            ops.atb(W[oi:, oi:oi + wi], W[oi:, :nc], S[:, :nc])          # C[R_i, :nc]: k >= o_i, one GEMM
+            if oi > 0:
+                ops.outer_minus(oi, wi, S, 0, oi, 2.0)
+            ops.outer_minus(oi, wi, S, oi, nc, 1.0)
+            part += ops.contract_rows(oi, wi, nc, S)
+        self._tick("lauum_contract", t0)
         t = torch.as_tensor(part)
         if g > 1:
             dev = getattr(ops, "device", torch.device("cpu"))
@@ -738,3 +743,9 @@ class ShardedLikelihood:
             dist.all_reduce(t, group=self.group)
             t = t.cpu()
         return value, 0.5 * t.numpy()
+
+    def _tick(self, name, t0):
+        if self.profile:
+            if hasattr(self.ops, "device") and self.ops.device.type == "cuda":
+                torch.cuda.synchronize(self.ops.device)
+            self.stats[name + "_ms"] = self.stats.get(name + "_ms", 0.0) + (time.perf_counter() - t0) * 1e3

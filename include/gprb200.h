@@ -184,6 +184,12 @@ int gprb200_potrf_panel_async_dev(gprb200_handle h, double* dP, int64_t ld, int6
 /* B <- L^-1 B (transposed = 0) or L^-T B (transposed != 0); L n x n lower (ldl), B n x M (ldb), dInvL as above. */
 int gprb200_trsm_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, double* dB,
                      int64_t ldb, int64_t M, int transposed);
+/* Columns of W = inv(L) (the TRTRI half of dpotri, include/LAPACKUtils.h:59-73) for the cyclic column blocks
+ * j = first, first + stride, ... of width col_block (a multiple of 128), stored compactly in dW (n x ldw): local column
+ * q * col_block + t is global column (first + q * stride) * col_block + t; rows above a column block are zero. The
+ * columns are independent, so g ranks with first = rank, stride = g split the n^3 / 3 flop without any exchange. */
+int gprb200_trtri_cols_dev(gprb200_handle h, const double* dL, int64_t ldl, const double* dInvL, int64_t n, int64_t col_block,
+                           int64_t first, int64_t stride, double* dW, int64_t ldw);
 /* 2 * sum_i log L(i,i) of an n x n device factor (replaces the determinant of lib/GaussianProcess.cpp:527) */
 int gprb200_logdet_dev(gprb200_handle h, const double* dL, int64_t ld, int64_t n, double* logdet);
 
@@ -226,11 +232,13 @@ int gprb200_dgram(gprb200_handle h, double* D_out);
  *   jac[i,p] = 0.5 tr((alpha_i alpha_i^T - C) dK/dtheta_p)       (M x P;   may be NULL)  (:335-341) */
 int gprb200_loglik(gprb200_handle h, int mode, double* value, double* grad, double* jac);
 /* Row-block share of the likelihood-gradient contraction (include/Likelihood.h:268-282 computes P full N x N products
- * for these traces): out[p] = sum_{i < nrows, j < N} dS[i * lds + j] * dK_p(x_{row0+i}, x_j), dS a DEVICE nrows x N
- * block of a symmetric weight matrix (e.g. rows of alpha alpha^T - C), dK generated on the fly, out P HOST doubles.
- * Summing the results of disjoint row blocks over ranks (ncclAllReduce of P doubles) gives tr(S dK_p). */
-int gprb200_dgram_contract_rows_dev(gprb200_handle h, int64_t row0, int64_t nrows, const double* dS, int64_t lds,
-                                    double* out);
+ * for these traces): out[p] = sum_{i < nrows, j < ncols} dS[i * lds + j] * dK_p(x_{row0+i}, x_j), dS a DEVICE
+ * nrows x ncols block of a symmetric weight matrix (e.g. rows of alpha alpha^T - C), dK generated on the fly, out P
+ * HOST doubles. ncols < N restricts the sum to the leading columns (the lower part of a symmetric matrix, whose
+ * strictly-lower blocks the caller weights twice). Summing disjoint row blocks over ranks (ncclAllReduce of P doubles)
+ * gives tr(S dK_p). */
+int gprb200_dgram_contract_rows_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_t ncols, const double* dS,
+                                    int64_t lds, double* out);
 /* q[k] = y_k^T (K + sigma^2 I)^-1 y_k, the data-fit term of include/Likelihood.h:175 (M values) */
 int gprb200_quadform(gprb200_handle h, double* q);
 

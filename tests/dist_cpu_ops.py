@@ -132,18 +132,25 @@ class CpuLikOps:
     def zeros(self, rows, cols):
         return torch.zeros((rows, cols), dtype=torch.float64)
 
-    def trtri_panel(self, o, w, out):
-        out.copy_(torch.as_tensor(sla.solve_triangular(self.L[o:, o:], out.numpy(), lower=True)))
+    def trtri_cols(self, first, stride, cb, ncl):
+        Wf = sla.solve_triangular(self.L, np.eye(self.N), lower=True)
+        W = np.zeros((self.N, ncl))
+        q = 0
+        for j in range(first, (self.N + cb - 1) // cb, stride):
+            w = min(cb, self.N - j * cb)
+            W[:, q * cb:q * cb + w] = Wf[:, j * cb:j * cb + w]
+            q += 1
+        return torch.as_tensor(W)
 
     def atb(self, A, B, out):
         out.copy_(torch.as_tensor(A.numpy().T @ B.numpy()))
 
-    def outer_minus(self, o, m, S):
-        S[:, :self.N] = torch.as_tensor(self.a[o:o + m] @ self.a.T) - S[:, :self.N]
+    def outer_minus(self, o, m, S, c0, c1, scale):
+        S[:, c0:c1] = scale * (torch.as_tensor(self.a[o:o + m] @ self.a[c0:c1].T) - S[:, c0:c1])
 
-    def contract_rows(self, o, m, S):
-        D = orc.kernel_derivative(self.k, self.X[o:o + m], self.X)      # (P, m, N)
-        return np.einsum("pij,ij->p", D, S.numpy()[:, :self.N])
+    def contract_rows(self, o, m, ncols, S):
+        D = orc.kernel_derivative(self.k, self.X[o:o + m], self.X[:ncols])      # (P, m, ncols)
+        return np.einsum("pij,ij->p", D, S.numpy()[:, :ncols])
 
     def close(self):
         pass
