@@ -35,7 +35,10 @@ struct GemmArgs {
     // ktri: triangular operand structure known to the caller; the k loop of a tile starts later (rounded down to BK):
     //   1: B (K x N) is lower triangular, B[k][n] = 0 for k < n  ->  k starts at the tile's first column (TRMM, NN)
     //   2: A and B (K x M, K x N) are lower triangular            ->  k starts at max(first row, first column) (LAUUM, TN)
+    //   3: as 1, but B's columns are a COMPACT selection of cyclic column blocks (trtri_cols, solve.cu): local column n
+    //      is global column (tri_first + (n / tri_cb) * tri_stride) * tri_cb + n % tri_cb, and B[k][n] = 0 for k < that
     int ktri;
+    int tri_cb, tri_first, tri_stride;
 };
 
 enum GemmForm { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };

@@ -178,7 +178,11 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
 
     const int64_t z = EXT ? blockIdx.y : 0;  // batch index
     // triangular operands: skip the leading k range that is known to be zero (whole BK steps only)
-    const int kskip = EXT ? (g.ktri == 1 ? n0 : (g.ktri == 2 ? max(m0, n0) : 0)) / BK * BK : 0;
+    const int kskip = EXT ? (g.ktri == 1 ? n0
+                                         : (g.ktri == 2 ? max(m0, n0)
+                                                        : (g.ktri == 3 ? (g.tri_first + (n0 / g.tri_cb) * g.tri_stride) * g.tri_cb + n0 % g.tri_cb
+                                                                       : 0))) / BK * BK
+                          : 0;
     const int Kt = EXT ? g.K - kskip : g.K;  // this tile's contraction depth
     const double* Abase = AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0);
     const double* Bbase = BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0);

@@ -607,8 +607,8 @@ static int inverse_long_k(Ctx* c, const double* L, int64_t ldl, const double* in
 // are independent, so g ranks that take first = rank, stride = g share the N^3 / 3 flop of the TRTRI with no exchange
 // (multi-GPU likelihood gradient, gpr_b200/dist.py: ShardedLikelihood). Same left-looking long-K sweep as the TRTRI half
 // of inverse_long_k; the local columns with a global index below a row r form a prefix of the compact matrix, so every
-// product is one GEMM on a contiguous column range. (The zero part above each column block is multiplied through:
-// the triangular k-skip of GemmArgs::ktri needs global column indices.)
+// product is one GEMM on a contiguous column range; the k loop of a tile skips the zero part above its column block
+// (GemmArgs::ktri = 3 maps the compact column of a tile to its global column).
 int trtri_cols(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t N, int64_t cb, int64_t first,
                int64_t stride, double* W, int64_t ldw) {
     const int64_t nblk = (N + cb - 1) / cb;
@@ -632,6 +632,7 @@ int trtri_cols(Ctx* c, const double* L, int64_t ldl, const double* invL, int64_t
             GemmArgs t{};
             t.A = L + s0 * ldl; t.lda = ldl; t.B = W; t.ldb = ldw; t.C = W + s0 * ldw; t.ldc = ldw;
             t.M = (int)ws; t.N = (int)n0; t.K = (int)s0; t.alpha = 1.0; t.beta = 0.0;
+            t.ktri = 3; t.tri_cb = (int)cb; t.tri_first = (int)first; t.tri_stride = (int)stride;   // skip k < global column
             GP_TRY(gemm(c, GEMM_NN, t));
         }
         for (int64_t r0 = s0; r0 < s0 + ws; r0 += NB) {
