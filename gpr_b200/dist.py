@@ -713,7 +713,10 @@ class ShardedLikelihood:
         Wloc = ops.trtri_cols(self.rank, g, m, ncl)
         if g > 1:
             Wg = torch.empty((g, N, ncl), dtype=torch.float64, device=Wloc.device)
-            dist.all_gather(list(Wg.unbind(0)), Wloc, group=self.group)
+            if Wloc.is_cuda:
+                dist.all_gather_into_tensor(Wg, Wloc, group=self.group)    # one NCCL all-gather, no staging copies
+            else:
+                dist.all_gather(list(Wg.unbind(0)), Wloc, group=self.group)
             self.stats["gathered_bytes"] += Wg.numel() * 8
         else:
             Wg = Wloc.unsqueeze(0)
