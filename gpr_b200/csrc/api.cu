@@ -45,7 +45,7 @@ namespace {
 struct PhaseTimer {
     Ctx* c;
     int phase;
-    cudaEvent_t e0, e1;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
     PhaseTimer(Ctx* c_, int p) : c(c_), phase(p) {
         cudaEventCreate(&e0);
         cudaEventCreate(&e1);
@@ -57,9 +57,16 @@ struct PhaseTimer {
         cudaEventSynchronize(e1);
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) c->phase_ms[phase] = ms;
-        cudaEventDestroy(e0);
-        cudaEventDestroy(e1);
+        release();
     }
+    void release() {
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+        e0 = e1 = nullptr;
+    }
+    ~PhaseTimer() { release(); }   // early returns between construction and resolve() must not leak the events
+    PhaseTimer(const PhaseTimer&) = delete;
+    PhaseTimer& operator=(const PhaseTimer&) = delete;
 };
 
 template <typename T>

@@ -39,6 +39,8 @@ struct SparseModel {
     double* dLS = nullptr;      // m x ldm  Cholesky factor of S
     double* dInvLS = nullptr;
     double* dAlpha = nullptr;   // m x ldy
+    int64_t alpha_ldy = 0;      // leading dimension dAlpha was allocated for (set_train may change M)
+    int d = 0;                  // dimension of the inducing points
     bool learned = false;
 };
 
@@ -82,14 +84,24 @@ int sparse_learn_core(Ctx* c, Tmp& knm) {
     if (m > n)
         return fail(c, -2, "SparseGaussianProcess::ComputeKernelVectorMatrix: number of dense samples must be higher than the "
                            "number of sparse samples");
+    if (s->d != c->d)
+        return fail(c, -2, "SparseGaussianProcess: the inducing points have dimension " + std::to_string(s->d) +
+                               " but the dense samples have dimension " + std::to_string(c->d));
     s->learned = false;
     const int64_t ldm = s->ldm, nblk = (m + NB - 1) / NB;
+    if (s->dAlpha && s->alpha_ldy != c->ldy) {   // a later set_train changed the number of label columns
+        cudaFree(s->dAlpha);
+        s->dAlpha = nullptr;
+    }
+    if (!s->dAlpha) {
+        GP_TRY(sp_alloc(c, &s->dAlpha, (size_t)m * c->ldy));
+        s->alpha_ldy = c->ldy;
+    }
     if (!s->dLK) {
         GP_TRY(sp_alloc(c, &s->dLK, (size_t)m * ldm));
         GP_TRY(sp_alloc(c, &s->dLS, (size_t)m * ldm));
         GP_TRY(sp_alloc(c, &s->dInvLK, (size_t)nblk * NB * NB));
         GP_TRY(sp_alloc(c, &s->dInvLS, (size_t)nblk * NB * NB));
-        GP_TRY(sp_alloc(c, &s->dAlpha, (size_t)m * c->ldy));
     }
     // K = k(Xm, Xm) + jitter I (ComputeKernelMatrixWithJitter, :175-180); S starts as a copy of it
     GP_TRY(gram_build(c, s->dXm, m, s->dXm, m, s->dLK, ldm, true, false, s->jitter));
@@ -346,6 +358,7 @@ int gprb200_sparse_set_inducing(gprb200_handle h, const double* Xm, int64_t m, i
     cudaStreamSynchronize(c->stream);
     sparse_free(s);
     s->m = m;
+    s->d = d;
     s->ldm = round_up(m, 16);
     s->jitter = jitter;
     GP_TRY(sp_alloc(c, &s->dXm, (size_t)m * d));

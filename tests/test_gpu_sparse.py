@@ -108,3 +108,37 @@ def test_sparse_gp_where_the_dense_matrix_would_not_fit():
     assert np.isfinite(mean).all() and np.isfinite(var).all() and (var > -1e-9).all()
     assert np.abs(mean[:, 0] - np.sin(3 * Xs[:, 0])).mean() <= 0.05        # it learned the function
     h.close()
+
+
+def test_set_train_with_more_label_columns_after_learn_reallocates(tmp_path):
+    """the sparse regression buffer was sized once; a later set_train with a wider label matrix (through the
+    C-ABI) must not overflow it, and an inducing-point dimension that no longer matches must be refused."""
+    import gpr_b200
+    rng = np.random.default_rng(3)
+    X = rng.uniform(-1, 1, (400, 3))
+    Xm = X[::10].copy()
+    h = gpr_b200.Handle(0)
+    ops, params = gpr_b200.KernelFactory.GetKernel("GaussianKernel(1.5,1,)").lower()
+    h.set_kernel(ops, params)
+    res = {}
+    for M in (1, 40, 3):
+        Y = np.tanh(X @ rng.standard_normal((3, M)))
+        h.set_train(X, Y, 0.3)
+        if M == 1:
+            h._ck(h.lib.gprb200_sparse_set_inducing(h.h, Xm.ctypes.data, Xm.shape[0], 3, 1e-2))
+        h._ck(h.lib.gprb200_sparse_learn(h.h))
+        a = np.empty((Xm.shape[0], M))
+        h._ck(h.lib.gprb200_sparse_get_alpha(h.h, a.ctypes.data))
+        # fresh handle with the same data: same regression vectors
+        h2 = gpr_b200.Handle(0)
+        h2.set_kernel(ops, params)
+        h2.set_train(X, Y, 0.3)
+        h2._ck(h2.lib.gprb200_sparse_set_inducing(h2.h, Xm.ctypes.data, Xm.shape[0], 3, 1e-2))
+        h2._ck(h2.lib.gprb200_sparse_learn(h2.h))
+        b = np.empty((Xm.shape[0], M))
+        h2._ck(h2.lib.gprb200_sparse_get_alpha(h2.h, b.ctypes.data))
+        h2.close()
+        assert np.array_equal(a, b), M
+    h.set_train(rng.uniform(-1, 1, (400, 2)), np.zeros((400, 1)), 0.3)      # dimension 2 now, inducing points are 3-d
+    assert h.lib.gprb200_sparse_learn(h.h) != 0 and "dimension" in h.lib.gprb200_last_error(h.h).decode()
+    h.close()
