@@ -242,6 +242,11 @@ def run_gpu(args):
                                ("host_io", args.skip_hostio, run_host_io), ("sparse", args.skip_sparse, run_sparse)):
             if not flag:
                 detail[name] = fn(torch, gpr_b200, local_rank)
+        if not args.skip_predict_loop:
+            detail["gp_predict_loop"] = run_predict_loop()
+            if "ms_per_point" in detail["gp_predict_loop"]:
+                line["config"]["gp_predict_loop"] = {k: detail["gp_predict_loop"][k] for k in
+                                                     ("N", "M", "ms_per_point", "predict_ms_per_point", "interval_ms_per_point")}
         if "loglik" in detail:
             line["config"]["loglik_iteration_ms"] = detail["loglik"]["value"]
             line["config"]["loglik_phase_ms"] = detail["loglik"]["phase_ms"]
@@ -616,6 +621,23 @@ def run_sharded_loglik(args, env, N=16384, iters=2):
             "collective": "all_gather of inv(L) column blocks (%.2f GB per iteration) + all_reduce of P doubles"
                           % (sl.stats["gathered_bytes"] / (iters + 1) * 1e-9),
             "grad": [float(x) for x in g], "grad_vs_1gpu": float(np.max(np.abs(g - np.array(one["grad"]))) / np.max(np.abs(g)))}
+
+
+def run_predict_loop(N=16384, d=8, M=4, T=200):
+    """The loop body of the reference's gpPredict (apps/GaussianProcessPredict.cpp:185-193) through the host C++ API
+    (libgplib.so): one gp->Predict(x) and one gp->GetCredibleInterval(x) per test point (tests/cxx/predict_loop_bench.cpp)."""
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "predict_loop_bench")
+    if not os.path.exists(exe):
+        return {"unavailable": "tests/cxx/bin/predict_loop_bench not built"}
+    try:
+        p = subprocess.run([exe, str(N), str(d), str(M), str(T)], capture_output=True, text=True, timeout=300)
+        if p.returncode != 0:
+            return {"unavailable": "predict_loop_bench failed: " + p.stderr[-300:]}
+        out = json.loads(p.stdout.strip().splitlines()[-1])
+        out["what"] = "gp->Predict(x) + gp->GetCredibleInterval(x), one test point per call, through libgplib.so"
+        return out
+    except Exception as e:
+        return {"unavailable": "predict_loop_bench: %s" % e}
 
 
 def run_predict(args, torch, gpr_b200, rank, local_rank, world, dev, barrier, max_over_ranks):
@@ -1000,6 +1022,7 @@ def main():
                     help="development only: ONE full-size warm-up pass at N > 1 GPUs instead of --warmup of them")
     ap.add_argument("--skip-replicas", action="store_true")
     ap.add_argument("--skip-predict-ci", action="store_true")
+    ap.add_argument("--skip-predict-loop", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-checks", action="store_true")
     args = ap.parse_args()

@@ -87,6 +87,8 @@ void free_model(Ctx* c) {
     cudaFree(c->dL); c->dL = nullptr;
     cudaFree(c->dInvL); c->dInvL = nullptr;
     cudaFree(c->dC); c->dC = nullptr;
+    cudaFree(c->dW); c->dW = nullptr;
+    c->have_winv = false;
     c->have_train = c->have_factor = c->have_alpha = c->have_core = c->core_is_loaded = false;
 }
 
@@ -198,6 +200,8 @@ int ensure_factor(Ctx* c) {
                         ")");
     GP_TRY(logdet_from_factor(c, c->dL, c->ldk, N, &c->logdet));
     c->have_factor = true;
+    c->have_winv = false;
+    c->ci_small_calls = 0;
     if (!c->core_is_loaded) c->have_core = false;
     return 0;
 }
@@ -263,6 +267,34 @@ int quad_forms(Ctx* c, const double* dXa, const double* dXb, int64_t T, double* 
         return 0;
     }
     GP_TRY(ensure_factor(c));
+    if (T <= 2 && c->opt_ci_winv && N > 2 * NB) {
+        // One or two test points per call (the loop of apps/GaussianProcessPredict.cpp:185-193): the forward
+        // substitution below is a latency-bound chain of N / 128 dependent steps per call. From the third such call
+        // on, inv(L) is formed once (N^3 / 3 flop) and every interval becomes one row-parallel, HBM-bound triangular
+        // matrix-vector product (trmv_lower_kernel).
+        ++c->ci_small_calls;
+        if (!c->have_winv && (c->opt_ci_winv >= 2 || c->ci_small_calls >= 3)) {
+            if (!c->dW) GP_TRY(dev_alloc(c, &c->dW, (size_t)N * c->ldk));
+            GP_TRY(trtri_cols(c, c->dL, c->ldk, c->dInvL, N, 512, 0, 1, c->dW, c->ldk));
+            c->have_winv = true;
+        }
+        if (c->have_winv) {
+            const int64_t ldkx = round_up(N, 16);
+            TempBuf Kx(c), V(c);
+            GP_TRY(Kx.alloc((size_t)2 * T * ldkx));
+            GP_TRY(V.alloc((size_t)N * 4));
+            GP_TRY(gram_build(c, dXa, T, c->dX, N, Kx.p, ldkx, false, false, 0.0));
+            GP_TRY(trmv_lower(c, c->dW, c->ldk, N, Kx.p, ldkx, (int)T, V.p, 2));
+            const double* vb = V.p;
+            if (!same) {
+                GP_TRY(gram_build(c, dXb, T, c->dX, N, Kx.p + T * ldkx, ldkx, false, false, 0.0));
+                GP_TRY(trmv_lower(c, c->dW, c->ldk, N, Kx.p + T * ldkx, ldkx, (int)T, V.p + 2 * N, 2));
+                vb = V.p + 2 * N;
+            }
+            GP_TRY(coldot(c, V.p, 2, vb, 2, N, T, d_q));
+            return 0;
+        }
+    }
     // V = L^-1 Kx^T with Kx^T generated directly as N x T; q = column dots
     const int64_t ldv = round_up(T, 16);
     TempBuf Va(c), Vb(c);
@@ -464,7 +496,7 @@ int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
         {"gram_lower_only", &h->opt_gram_lower_only}, {"gram_terms", &h->opt_gram_terms}, {"stream_io", &h->opt_stream_io}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead}, {"chol_left", &h->opt_chol_left},
-        {"gemm_stages", &h->opt_gemm_stages}, {"panel_split", &h->opt_panel_split}, {"gemm_small", &h->opt_gemm_small}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
+        {"gemm_stages", &h->opt_gemm_stages}, {"ci_winv", &h->opt_ci_winv}, {"panel_split", &h->opt_panel_split}, {"gemm_small", &h->opt_gemm_small}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
         {"profile", &h->opt_profile}};
     if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
     for (auto& o : opts)
@@ -937,10 +969,16 @@ int gprb200_posterior_cov(gprb200_handle h, const double* Xa, const double* Xb, 
     GP_TRY(q.alloc((size_t)T));
     GP_TRY(ks.alloc((size_t)T));
     GP_TRY(out.alloc((size_t)T));
+    // gp(x, x) (GetCredibleInterval, lib/GaussianProcess.cpp:108): one kernel vector and one solve instead of two
+    const bool same = (Xa == Xb) || memcmp(Xa, Xb, sizeof(double) * T * c->d) == 0;
     GP_CUDA(c, cudaMemcpyAsync(xa.p, Xa, sizeof(double) * T * c->d, cudaMemcpyHostToDevice, c->stream));
-    GP_CUDA(c, cudaMemcpyAsync(xb.p, Xb, sizeof(double) * T * c->d, cudaMemcpyHostToDevice, c->stream));
-    GP_TRY(quad_forms(c, xa.p, xb.p, T, q.p));
-    GP_TRY(kpair_values(c, xa.p, xb.p, T, ks.p));
+    const double* xbp = xa.p;
+    if (!same) {
+        GP_CUDA(c, cudaMemcpyAsync(xb.p, Xb, sizeof(double) * T * c->d, cudaMemcpyHostToDevice, c->stream));
+        xbp = xb.p;
+    }
+    GP_TRY(quad_forms(c, xa.p, xbp, T, q.p));
+    GP_TRY(kpair_values(c, xa.p, xbp, T, ks.p));
     ci_finish_kernel<<<(unsigned)((T + 255) / 256), 256, 0, c->stream>>>(ks.p, q.p, T, out.p, 0);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());

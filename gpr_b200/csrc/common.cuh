@@ -65,6 +65,10 @@ struct Ctx {
     int64_t ldk = 0;
     double* dInvL = nullptr;  // ceil(N/NB) blocks of NB x NB: inverses of the diagonal blocks of L
     double* dC = nullptr;     // N x ldk explicit core matrix (lazy)
+    double* dW = nullptr;     // N x ldk inverse factor inv(L) (lazy; single-point credible intervals, api.cu: quad_forms)
+    bool have_winv = false;
+    int64_t ci_small_calls = 0;   // single-point interval calls since the last factorisation
+    int64_t opt_ci_winv = 1;      // 0: never form inv(L); 1: from the 3rd single-point call; 2: at the first
     int* dInfo = nullptr;
     double* dScratch = nullptr;  // small reductions
     size_t scratch_bytes = 0;
@@ -192,6 +196,7 @@ int stream_d2h(Ctx* c, double* flat, int64_t ldf, const double* src, int64_t lds
 void hostio_destroy(Ctx* c);
 // predict.cu
 int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, int64_t M, double* out);
+int trmv_lower(Ctx* c, const double* W, int64_t ldw, int64_t N, const double* kx, int64_t ldk, int T, double* V, int64_t ldv);
 
 }  // namespace gprb200
 

@@ -121,6 +121,58 @@ int gemv_t(Ctx* c, const double* kx, const double* A, int64_t lda, int64_t N, in
     return 0;
 }
 
+// ---- trmv_lower: V (N x T, T <= 2) = W Kx^T for a lower-triangular W (the explicit inverse factor) ---------------------
+// Single-point credible interval (GetCredibleInterval, lib/GaussianProcess.cpp:103-114, called once per test point by
+// apps/GaussianProcessPredict.cpp:188): v = inv(L) kx used to be a forward substitution, a chain of N / 128 dependent
+// block steps (0.76 ms at N = 16384, latency-bound). With W = inv(L) formed once it is a matrix-vector product with no
+// dependence between rows: one warp per row, 16-byte loads, only the non-zero prefix k <= i of each row is read
+// (4 N^2 bytes in total: HBM-bound, 1.07 GB = ~0.15 ms at N = 16384). kx is T x ldk (the cross-Gram layout).
+template <int T>
+__global__ void __launch_bounds__(256) trmv_lower_kernel(const double* __restrict__ W, int64_t ldw, int64_t N,
+                                                          const double* __restrict__ kx, int64_t ldk, double* __restrict__ V,
+                                                          int64_t ldv) {
+    const int lane = threadIdx.x & 31;
+    // long rows first: the last CTAs to start get the short rows
+    const int64_t i = N - 1 - ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5));
+    if (i < 0) return;
+    const double* w = W + i * ldw;
+    double s[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) s[t] = 0.0;
+    const int64_t n2 = (i + 1) & ~(int64_t)1;   // even prefix, 16-byte loads (W rows are 16-byte aligned, ldw even)
+    for (int64_t k = lane * 2; k < n2; k += 64) {
+        const double2 a = ld_stream(reinterpret_cast<const double2*>(w + k));
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const double2 b = *reinterpret_cast<const double2*>(kx + t * ldk + k);
+            s[t] = fma(a.x, b.x, s[t]);
+            s[t] = fma(a.y, b.y, s[t]);
+        }
+    }
+    if (lane == 0 && n2 <= i) {
+#pragma unroll
+        for (int t = 0; t < T; ++t) s[t] = fma(w[i], kx[t * ldk + i], s[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s[t] += __shfl_xor_sync(0xffffffffu, s[t], o);
+        if (lane == 0) V[i * ldv + t] = s[t];
+    }
+}
+
+int trmv_lower(Ctx* c, const double* W, int64_t ldw, int64_t N, const double* kx, int64_t ldk, int T, double* V, int64_t ldv) {
+    if (T < 1 || T > 2) return fail(c, -2, "trmv_lower: 1 or 2 vectors");
+    if ((ldw & 1) || (ldk & 1) || (reinterpret_cast<uintptr_t>(W) & 15) || (reinterpret_cast<uintptr_t>(kx) & 15))
+        return fail(c, -2, "trmv_lower: operands must be 16-byte aligned with even leading dimensions");
+    const unsigned grid = (unsigned)((N + 7) / 8);
+    if (T == 1) trmv_lower_kernel<1><<<grid, 256, 0, c->stream>>>(W, ldw, N, kx, ldk, V, ldv);
+    else trmv_lower_kernel<2><<<grid, 256, 0, c->stream>>>(W, ldw, N, kx, ldk, V, ldv);
+    ++c->launches;
+    GP_CUDA(c, cudaGetLastError());
+    return 0;
+}
+
 // ---- allocation-free variant of gemv_t (gprb200_gemv_t_noalloc_dev, include/gprb200.h) -------------------------------
 // The row-split partial sums live in a file-scope device array instead of a cudaMallocAsync buffer, for callers that
 // cannot allocate (CUDA graph capture, tight serving loops). GV_SCRATCH_DOUBLES doubles = 32 MiB are held by every GPU
