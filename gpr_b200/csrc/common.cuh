@@ -78,6 +78,8 @@ struct Ctx {
     double logdet = 0.0;
 
     int64_t opt_gram_lower_only = 1;
+    int64_t opt_gram_mma = 1;         // r^2 = |x|^2 + |y|^2 - 2 x.y with the cross term on DMMA for large d (gram_mma.cu)
+    int64_t opt_gram_mma_min_d = 32;  // ... from this input dimension
     int64_t opt_gram_terms = 2;   // value Gram: 2 row-group kernel (gram_rows_kernel), 1 per-tile term form, 0 interpreter
     int64_t opt_nbo = 0;          // outer (trailing-update) block of the two-level Cholesky; 0 = auto (512 / 1024)
     int64_t opt_chol_left = 0;    // left-looking outer loop (long-K column updates): measured slower, see potrf.cu

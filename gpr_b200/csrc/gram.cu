@@ -13,6 +13,9 @@
 
 namespace gprb200 {
 
+int gram_build_mma(Ctx* c, const DevProg& P, const double* Xa, int64_t Na, const double* Xb, int64_t Nb, double* out,
+                   int64_t ldo, bool symmetric, bool lower_only, double diag_add, int* d_nonfinite);
+
 constexpr int GT = 64;        // CTA tile is GT x GT entries
 constexpr int GDC = 8;        // dimensions staged per shared-memory chunk
 constexpr int GTHREADS = 256;
@@ -1246,6 +1249,10 @@ int gram_build(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64_t N
                bool symmetric, bool lower_only, double diag_add, int* d_nonfinite) {
     DevProg P;
     if (int r = lower_program(c->prog, &P, &c->err)) return r;
+    {   // large input dimension: cross term of r^2 on the FP64 tensor pipe (gram_mma.cu); 1 = does not apply
+        const int r = gram_build_mma(c, P, Xa, Na, Xb, Nb, out, ldo, symmetric, lower_only, diag_add, d_nonfinite);
+        if (r <= 0) return r;
+    }
     GramArgs a{};
     a.Xa = Xa; a.Xb = Xb; a.Na = Na; a.Nb = Nb; a.d = c->d;
     a.out = out; a.ldo = ldo;

@@ -1,0 +1,84 @@
+"""-m gpu: N1 - the Gram matrix for a large input dimension with the cross term of r^2 = |x|^2 + |y|^2 - 2 x.y on the
+FP64 tensor pipe (gpr_b200/csrc/gram_mma.cu) against the oracle's direct evaluation of include/Kernel.h, at the
+reference's own dimensions: d = 30 (BASELINE config C2, GaussianKernel(1.5 sqrt(30), 1)) and d = 238
+(scripts/params/pmb/config_ZL0001_vol01.yaml:49-52: GaussianKernel(35, 30), n_inputModes 238).
+Bar: |K - K_oracle| <= 1e-13 max |K| element-wise, the same as the direct-difference kernels."""
+import math
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_K(ks, A, B, chunk=64):
+    from oracle import gpr_oracle as orc
+    k = orc.parse_kernel(ks)
+    return np.concatenate([orc.kernel_matrix(k, A[i:i + chunk], B) for i in range(0, len(A), chunk)], axis=0)
+
+
+def _handle(ks, X, Y, sigma, mma):
+    import gpr_b200
+    h = gpr_b200.Handle(0)
+    ops, params = gpr_b200.KernelFactory.GetKernel(ks).lower()
+    h.set_kernel(ops, params)
+    h.set_option("gram_mma", mma)
+    h.set_train(X, Y, sigma)
+    return h
+
+
+CASES = [
+    ("c2_d30", "GaussianKernel(%.17g,1,)" % (1.5 * math.sqrt(30.0)), 30, 1.0, 1100),
+    ("prod_d238", "GaussianKernel(35,30,)", 238, 3.0, 900),
+    ("rq_white_d64", "SumKernel(RationalQuadraticKernel(1.2,9,2,),WhiteKernel(0.3,))", 64, 1.0, 777),
+    ("product_d48", "ProductKernel(GaussianKernel(8,1.1,),RationalQuadraticKernel(0.9,12,1.5,))", 48, 1.0, 640),
+    ("gaussexp_d40", "SumKernel(GaussianExpKernel(2.2,0.1,),GaussianKernel(7,0.5,))", 40, 1.0, 513),
+]
+
+
+@pytest.mark.parametrize("name,ks,d,xscale,N", CASES, ids=[c[0] for c in CASES])
+def test_tensor_core_gram_matches_oracle(name, ks, d, xscale, N):
+    rng = np.random.default_rng(len(name) + d)
+    X = xscale * rng.standard_normal((N, d)) + 0.7          # a non-zero mean: the centring matters
+    X[-5:] = X[:5]                                          # exact duplicates: WhiteKernel's ||x - y|| == 0 off the diagonal
+    X[-6] = X[6] + 1e-9                                     # a near-coincident pair: the direct-difference fix-up
+    Y = np.tanh(X[:, :2])
+    Kref = _oracle_K(ks, X, X)
+    scale = np.abs(Kref).max()
+    h = _handle(ks, X, Y, 1.0, 1)
+    n0 = h.launch_count()
+    K = h.gram(False)                                       # symmetric full K (ComputeKernelMatrix)
+    assert h.launch_count() - n0 >= 4                       # centre + norms + GEMM + transform: the DMMA path ran
+    assert np.abs(K - Kref).max() <= 1e-13 * scale
+    assert np.array_equal(K, K.T)
+    Xs = xscale * rng.standard_normal((200, d)) + 0.7
+    Kx = h.kernel_vector(Xs)                                # 200 x N cross-Gram
+    assert np.abs(Kx - _oracle_K(ks, Xs, X)).max() <= 1e-13 * scale
+    h.learn(0)                                              # lower-triangle build inside Learn
+    a1 = h.alpha()
+    h.close()
+    h0 = _handle(ks, X, Y, 1.0, 0)                          # the direct-difference kernels on the same inputs
+    K0 = h0.gram(False)
+    assert np.abs(K - K0).max() <= 2e-13 * scale
+    h0.learn(0)
+    assert np.abs(a1 - h0.alpha()).max() <= 1e-9 * np.abs(a1).max()
+    h0.close()
+
+
+def test_cancellation_guard_falls_back_to_direct_differences():
+    """|x|^2 / sigma^2 too large for the expansion to keep 1e-13: the call must take the direct kernels (and stay exact)."""
+    rng = np.random.default_rng(7)
+    N, d = 600, 64
+    X = 1000.0 * rng.standard_normal((N, d))
+    X[1] = X[0] + 0.05 * rng.standard_normal(d)             # a pair at distance ~0.4 among norms ~8000
+    ks = "GaussianKernel(0.5,1,)"
+    Y = np.zeros((N, 1))
+    h = _handle(ks, X, Y, 1.0, 1)
+    n0 = h.launch_count()
+    K = h.gram(False)
+    launches = h.launch_count() - n0
+    Kref = _oracle_K(ks, X, X)
+    assert np.abs(K - Kref).max() <= 1e-13
+    assert K[1, 0] > 1e-3                                   # the close pair is resolved, not rounded away
+    assert launches <= 4                                    # norms (guard) + one direct Gram kernel, no GEMM + transform
+    h.close()
