@@ -79,7 +79,7 @@ struct Ctx {
 
     int64_t opt_gram_lower_only = 1;
     int64_t opt_gram_mma = 1;         // r^2 = |x|^2 + |y|^2 - 2 x.y with the cross term on DMMA for large d (gram_mma.cu)
-    int64_t opt_gram_mma_min_d = 32;  // ... from this input dimension
+    int64_t opt_gram_mma_min_d = 64;  // ... from this input dimension (measured: d = 30 6.5 vs 4.0 ms direct, d = 64 7.4 vs 8.4, d = 238 13.0 vs 41.7)
     int64_t opt_gram_terms = 2;   // value Gram: 2 row-group kernel (gram_rows_kernel), 1 per-tile term form, 0 interpreter
     int64_t opt_nbo = 0;          // outer (trailing-update) block of the two-level Cholesky; 0 = auto (512 / 1024)
     int64_t opt_chol_left = 0;    // left-looking outer loop (long-K column updates): measured slower, see potrf.cu

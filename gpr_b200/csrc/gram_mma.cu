@@ -6,7 +6,7 @@
 // d = 8 (BASELINE configs C3-C5) that is nothing next to the exponential, at d = 30 (C2) it is half of the pair, and at
 // the reference's production setting d = 238 (scripts/params/pmb/config_ZL0001_vol01.yaml:49-52, n_inputModes) it IS
 // the pair: 2 N^2 d flop, a real contraction, which DMMA.8x8x4 runs at twice the FMA-pipe rate with none of the issue
-// slots. Used for d >= 32 (option "gram_mma_min_d") when the tree has no PERIODIC leaf.
+// slots. Used for d >= 64 (option "gram_mma_min_d"; measured crossover, tools/gram_mma_probe.py) when the tree has no PERIODIC leaf.
 //
 // Steps (all on c->stream):
 //   1. centre: xc = x - mean(Xb) (r^2 is translation invariant; smaller norms = less cancellation), row norms n_i;

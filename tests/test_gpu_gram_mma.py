@@ -23,6 +23,7 @@ def _handle(ks, X, Y, sigma, mma):
     ops, params = gpr_b200.KernelFactory.GetKernel(ks).lower()
     h.set_kernel(ops, params)
     h.set_option("gram_mma", mma)
+    h.set_option("gram_mma_min_d", 16)      # the default threshold is 64 (measured crossover); C2's d = 30 is tested through the same path
     h.set_train(X, Y, sigma)
     return h
 
