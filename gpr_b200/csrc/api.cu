@@ -496,7 +496,7 @@ int gprb200_set_option(gprb200_handle h, const char* name, int64_t value) {
     if (!h || !name) return -2;
     struct { const char* n; int64_t* p; } opts[] = {
         {"gram_lower_only", &h->opt_gram_lower_only}, {"gram_mma", &h->opt_gram_mma}, {"gram_mma_min_d", &h->opt_gram_mma_min_d}, {"gram_terms", &h->opt_gram_terms}, {"stream_io", &h->opt_stream_io}, {"nbo", &h->opt_nbo}, {"lookahead", &h->opt_lookahead}, {"chol_left", &h->opt_chol_left},
-        {"gemm_stages", &h->opt_gemm_stages}, {"ci_winv", &h->opt_ci_winv}, {"panel_split", &h->opt_panel_split}, {"gemm_small", &h->opt_gemm_small}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
+        {"gemm_stages", &h->opt_gemm_stages}, {"gemm_tma", &h->opt_gemm_tma}, {"gemm_tma_min_k", &h->opt_gemm_tma_min_k}, {"gemm_tma_min_tiles", &h->opt_gemm_tma_min_tiles}, {"ci_winv", &h->opt_ci_winv}, {"panel_split", &h->opt_panel_split}, {"gemm_small", &h->opt_gemm_small}, {"gemm_variant", &h->opt_gemm_variant}, {"skinny", &h->opt_skinny}, {"potrf_tile", &h->opt_potrf_tile}, {"solve_left_min_m", &h->opt_solve_left_min_m}, {"inverse_long_k", &h->opt_inverse_long_k}, {"trsv_chain", &h->opt_trsv_chain},
         {"profile", &h->opt_profile}};
     if (!strcmp(name, "profile")) h->prof_gemv_ms = h->prof_gemv_bytes = h->prof_gemv_launches = 0.0;
     for (auto& o : opts)

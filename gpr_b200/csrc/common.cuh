@@ -88,6 +88,9 @@ struct Ctx {
     int64_t opt_skinny = 1;        // route n <= 8 NN/TN products to the streaming kernels of skinny.cu
     int64_t opt_gemm_variant = -1; // -1: auto; 0: 64x32 warp tiles (8 warps/SM), 1: 64x16 warp tiles (16 warps/SM)
     int64_t opt_gemm_stages = 3;  // cp.async ring depth of the 128x64 GEMM
+    int64_t opt_gemm_tma = 0;            // 1: persistent TMA-fed kernel (dgemm_tma.cu) for large NT products (A/B: no gain)
+    int64_t opt_gemm_tma_min_k = 256;    // ... from this contraction depth
+    int64_t opt_gemm_tma_min_tiles = 64; // ... and this many 128 x 128 output tiles
     int64_t opt_trsv_chain = 1;           // M <= 2 triangular solves as one chained launch (solve.cu)
     int64_t opt_inverse_long_k = 1;       // explicit inverse as TRTRI + LAUUM with long-K GEMMs (solve.cu)
     int64_t opt_solve_left_min_m = 8192;  // left-looking (long-K) triangular solves from this many RHS
@@ -159,6 +162,9 @@ int dgram_build_xy(Ctx* c, const double* Xa, int64_t Na, const double* Xb, int64
 // dgemm.cu
 int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream = nullptr);
 int gemm_skinny(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream);  // skinny.cu, n <= 8
+// dgemm_tma.cu: persistent TMA + mbarrier producer / DMMA consumers, NT form
+bool gemm_tma_eligible(const Ctx* c, GemmForm form, const GemmArgs& g);
+int gemm_tma_nt(Ctx* c, const GemmArgs& g, cudaStream_t stream);
 // potrf.cu
 int potrf_blocked(Ctx* c, double* A, int64_t ld, int64_t N, double* invL, int* info_host);
 int potrf_panel(Ctx* c, double* P, int64_t ld, int64_t rows, int64_t w, double* invL, int col0, int* info_host);

@@ -23,6 +23,7 @@
 // mod 128), so those four 32-byte pieces always fall in four different bank groups: 2 wavefronts per LDS, the
 // minimum. (Round-1 ncu showed 4 per LDS with a (row & 7) 16-byte swizzle and the shared-memory pipe at 90 %.)
 #include "common.cuh"
+#include "gemm_tile_map.cuh"
 
 namespace gprb200 {
 
@@ -121,36 +122,6 @@ struct FastLoader {
         for (int i = 0; i < NI; ++i) cp_async16_full(dst + stage_bytes + i * SSTRIDE, p + i * gstride);
     }
 };
-
-// linear block index -> (ti, tj), rasterised for L2 reuse: CTAs are issued in groups of GM tile-rows, column-major
-// inside a group, so the ~300 co-resident CTAs share GM A-panels and a few dozen B-panels (a ~25 MB working set at
-// K = 1024) instead of one A-panel and ~300 B-panels (150 MB > L2), which made the SYRK update re-read its panel
-// 7x from DRAM in 128-byte pieces at a 256 KB stride (profiles/r01_ncu_summary.md).
-// lower: group g holds tile-rows [g GM, (g+1) GM) and R GM (g+1) tile-columns (R = BM / BN); tiles right of the
-// diagonal and rows past the edge exit at once.
-constexpr int GM = 8;
-template <int BM, int BN>
-__device__ __forceinline__ bool map_tile(int lin, int lower, int tiles_m, int tiles_n, int& ti, int& tj) {
-    if (!lower) {
-        const int width = GM * tiles_n;
-        const int group = lin / width;
-        const int first = group * GM;
-        const int gsize = min(tiles_m - first, GM);
-        const int local = lin - group * width;
-        ti = first + local % gsize;
-        tj = local / gsize;
-        return true;
-    }
-    constexpr int R = BM / BN;
-    constexpr int64_t Q = (int64_t)GM * GM * R;  // tiles of group g: Q (g + 1); prefix(g) = Q g (g + 1) / 2
-    int gidx = (int)((sqrt(1.0 + 8.0 * (double)lin / (double)Q) - 1.0) * 0.5);
-    while (Q * (gidx + 1) * (gidx + 2) / 2 <= lin) ++gidx;
-    while (Q * gidx * (gidx + 1) / 2 > lin) --gidx;
-    const int local = lin - (int)(Q * gidx * (gidx + 1) / 2);
-    ti = gidx * GM + local % GM;
-    tj = local / GM;
-    return ti < tiles_m && tj < tiles_n && (int64_t)tj * BN <= (int64_t)ti * BM + BM - 1;
-}
 
 // STAGES k-tiles of BK live in the shared-memory ring; KSTEP of them are consumed per CTA barrier
 // (KSTEP = 2 halves the barrier rate at the same BK = 16 tile geometry).
@@ -337,6 +308,7 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
         return gemm_skinny(c, form, g, stream);
     if (!aligned16(g.A) || !aligned16(g.B) || !aligned16(g.C) || (g.lda & 1) || (g.ldb & 1) || (g.ldc & 1))
         return fail(c, -2, "gemm: operands must be 16-byte aligned with even leading dimensions");
+    if (gemm_tma_eligible(c, form, g)) return gemm_tma_nt(c, g, stream);
     if (g.lower && g.M != g.N) return fail(c, -2, "gemm: lower-only update needs a square C");
     // wide tile (128x128, 8 warps) when C has a single column tile that must be owned by one CTA
     // (in-place panel solves), otherwise 128x64 tiles with two CTAs per SM so one CTA's epilogue
