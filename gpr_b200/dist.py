@@ -504,10 +504,10 @@ class BlockCyclicGP:
                     acc[self.roff[k]:self.roff[k] + w].copy_(buf)
             # ---- every rank gets the whole alpha: each block row is contributed by grid column 0 of its grid row
             out = ops.zeros(self.N, ld)
-            if self.pc == 0:
+            if self.pc == 0 or self.Pr == 1:    # with Pr = 1 every rank already holds every block row
                 for i in self.myrows:
                     out[i * nb:i * nb + self.hgt[i]].copy_(acc[self.roff[i]:self.roff[i] + self.hgt[i]])
-            if self.Pr > 1:     # with Pr = 1 every rank already holds every block row
+            if self.Pr > 1:
                 dist.all_reduce(out, group=self.group)
                 self.stats["collectives"] += 1
         return out[:, :M]
