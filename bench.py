@@ -444,55 +444,94 @@ def headline_c5(args, env, detail):
     X = rng.uniform(-1, 1, (N, C3_D))
     Y = (np.sin(3.0 * X[:, :1]) + 0.5 * np.cos(2.0 * X[:, 1:2] + X[:, 2:3]) + 0.1 * rng.standard_normal((N, 1)))
     ops_, params = gpr_b200.KernelFactory.GetKernel(C3_KERNEL).lower()
-    ops = gd.DeviceOps(local_rank, ops_, params, X, C3_SIGMA)
-    warm = gd.BlockCyclicGP(ops, 8192, nb=nb, grid=grid)     # communicators, allocator, kernel attributes
-    warm.learn(Y[:8192])
-    del warm
-    torch.cuda.empty_cache()
-    gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid)
-    Yd = torch.from_numpy(Y).to(dev)
-    for _ in range(1 if args.large_quick_warmup else args.warmup):
-        gp.learn(Yd)
-    env["barrier"]()
-    sampler = ClockSampler(local_rank)
-    l0 = ops.h.launch_count() + ops.hp.launch_count()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-    tsum = np.zeros(4)
-    info, alpha = 0, None
-    for _ in range(args.steps):
-        with ops.on("main"):
-            ev[0].record()
-        gp.build_gram()
-        with ops.on("main"):
-            ev[1].record()
-        info = gp.factor()
-        with ops.on("main"):
-            ev[2].record()
-        alpha = gp.solve(Yd) if info == 0 else None
-        with ops.on("main"):
-            ev[3].record()
+    impl = args.c5_impl
+    if impl == "capi":
+        # the whole schedule under the C-ABI (libgprb200_dist.so, NCCL from C++): every step takes HOST X, Y and returns a
+        # HOST alpha, so one loop gives both the device-timed value (the library's CUDA events) and the end-to-end time
+        from gpr_b200 import capi_dist
+        dh = capi_dist.DistHandle(local_rank, rank, world, capi_dist.exchange_id(), grid)
+        dh.set_kernel(ops_, params)
+        dh.learn(X[:8192], Y[:8192], C3_SIGMA, nb=nb)          # communicators, kernel attributes
+        for _ in range(1 if args.large_quick_warmup else args.warmup):
+            dh.learn(X, Y, C3_SIGMA, nb=nb)
+        env["barrier"]()
+        sampler = ClockSampler(local_rank)
+        tsum = np.zeros(4)
+        wall, launches, info, logdet, alpha_host = 0.0, 0, 0, None, None
+        stats = {"bcast_bytes": 0.0, "collectives": 0.0}
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            alpha_host, logdet = dh.learn(X, Y, C3_SIGMA, nb=nb)
+            wall += time.perf_counter() - t0
+            ph, c = dh.phase_ms(), dh.counters()
+            tsum += np.array([ph["gram"], ph["factor"], ph["solve"], ph["gram"] + ph["factor"] + ph["solve"]])
+            launches += int(c["launches"])
+            stats["bcast_bytes"] += c["bytes"]
+            stats["collectives"] += c["collectives"]
+        env["barrier"]()
+        clocks = sampler.stop()
+        t = torch.tensor(tsum, dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gram_ms, factor_ms, solve_ms, total_ms = (float(v) / args.steps for v in t.tolist())
+        e2e_steps = args.steps
+        e2e_ms = env["max_over_ranks"](wall * 1e3) / e2e_steps
+        per_learn = args.steps
+        alpha = None
+        dh.close()
+    else:
+        ops = gd.DeviceOps(local_rank, ops_, params, X, C3_SIGMA)
+        warm = gd.BlockCyclicGP(ops, 8192, nb=nb, grid=grid)     # communicators, allocator, kernel attributes
+        warm.learn(Y[:8192])
+        del warm
+        torch.cuda.empty_cache()
+        gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid)
+        Yd = torch.from_numpy(Y).to(dev)
+        for _ in range(1 if args.large_quick_warmup else args.warmup):
+            gp.learn(Yd)
+        env["barrier"]()
+        sampler = ClockSampler(local_rank)
+        l0 = ops.h.launch_count() + ops.hp.launch_count()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        tsum = np.zeros(4)
+        info, alpha = 0, None
+        for _ in range(args.steps):
+            with ops.on("main"):
+                ev[0].record()
+            gp.build_gram()
+            with ops.on("main"):
+                ev[1].record()
+            info = gp.factor()
+            with ops.on("main"):
+                ev[2].record()
+            alpha = gp.solve(Yd) if info == 0 else None
+            with ops.on("main"):
+                ev[3].record()
+            torch.cuda.synchronize()
+            tsum += np.array([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]),
+                              ev[0].elapsed_time(ev[3])])
+        env["barrier"]()
+        clocks = sampler.stop()
+        launches = ops.h.launch_count() + ops.hp.launch_count() - l0
+        t = torch.tensor(tsum, dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gram_ms, factor_ms, solve_ms, total_ms = (float(v) / args.steps for v in t.tolist())
+        stats = dict(gp.stats)
+        # end to end: host X, Y in, host alpha out (pageable), every step
+        e2e_steps = min(args.steps, 2)
+        alpha_host = None
+        env["barrier"]()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ops.set_samples(X, C3_SIGMA)
+            gp.build_gram()
+            if gp.factor() == 0:
+                alpha_host = gp.solve(Y).cpu().numpy()
         torch.cuda.synchronize()
-        tsum += np.array([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]),
-                          ev[0].elapsed_time(ev[3])])
-    env["barrier"]()
-    clocks = sampler.stop()
-    launches = ops.h.launch_count() + ops.hp.launch_count() - l0
-    t = torch.tensor(tsum, dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    gram_ms, factor_ms, solve_ms, total_ms = (float(v) / args.steps for v in t.tolist())
-    stats = dict(gp.stats)
-    # end to end: host X, Y in, host alpha out (pageable), every step
-    e2e_steps = min(args.steps, 2)
-    alpha_host = None
-    env["barrier"]()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ops.set_samples(X, C3_SIGMA)
-        gp.build_gram()
-        if gp.factor() == 0:
-            alpha_host = gp.solve(Y).cpu().numpy()
-    torch.cuda.synchronize()
-    e2e_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3) / e2e_steps
+        e2e_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3) / e2e_steps
+        per_learn = max(1, args.steps + e2e_steps + 1)
+        logdet = gp.logdet
+        ops.close()
+        del gp, Yd
     resid = None
     if info == 0 and rank == 0 and not args.skip_checks:
         resid = residual_rows(C3_KERNEL, X, Y, alpha_host if alpha_host is not None else alpha.cpu().numpy(), C3_SIGMA, nrows=96)
@@ -512,9 +551,11 @@ def headline_c5(args, env, detail):
             "useful_flops": flops, "l2": "inputs larger than L2 (%.0f GB per GPU)" % (4.0 * N * N / world * 1e-9),
             "learn_s": total_ms * 1e-3, "gram_s": gram_ms * 1e-3, "cholesky_s": factor_ms * 1e-3, "solve_s": solve_ms * 1e-3,
             "cholesky_tflops_total": chol_tf, "cholesky_frac_of_peak": chol_tf / (FP64_PEAK_TFLOPS * world),
-            "bcast_GB_per_rank": stats["bcast_bytes"] * 1e-9 / max(1, args.steps + e2e_steps + 1),
-            "collectives_per_learn": stats["collectives"] / max(1, args.steps + e2e_steps + 1),
-            "info": info, "logdet": gp.logdet, "rel_residual_rows": resid,
+            "bcast_GB_per_rank": stats["bcast_bytes"] * 1e-9 / per_learn,
+            "collectives_per_learn": stats["collectives"] / per_learn,
+            "impl": "libgprb200_dist.so: schedule and NCCL calls in C++ under the C-ABI (include/gprb200_dist.h)" if impl == "capi"
+                    else "gpr_b200.dist.BlockCyclicGP: torch.distributed schedule over the single-GPU C-ABI",
+            "info": info, "logdet": logdet, "rel_residual_rows": resid,
             "residual_note": "96 sampled rows, kernel rows evaluated by the CPU oracle",
             "warmup_note": "DEVELOPMENT RUN: 1 full-size warm-up pass only" if args.large_quick_warmup
                            else "%d full-size warm-up passes" % args.warmup,
@@ -533,8 +574,6 @@ def headline_c5(args, env, detail):
             "peak_source": "37.1 = measured DMMA issue rate (profiles/r01_fp64_probe.txt)",
         },
     }
-    ops.close()
-    del gp, Yd
     torch.cuda.empty_cache()
     return line
 
@@ -1018,6 +1057,8 @@ def main():
     ap.add_argument("--large-n", type=int, default=131072)
     ap.add_argument("--large-nb", type=int, default=1024, help="block-column width of the block-cyclic Cholesky")
     ap.add_argument("--grid", default="", help="PrxPc process grid of the block-cyclic Cholesky (default: dist.default_grid)")
+    ap.add_argument("--c5-impl", choices=["capi", "torch"], default="capi",
+                    help="N>1 headline: capi = libgprb200_dist.so (schedule + NCCL in C++), torch = gpr_b200.dist.BlockCyclicGP")
     ap.add_argument("--large-quick-warmup", action="store_true",
                     help="development only: ONE full-size warm-up pass at N > 1 GPUs instead of --warmup of them")
     ap.add_argument("--skip-replicas", action="store_true")

@@ -126,7 +126,7 @@ class DistHandle:
         return {k: self.lib.gprb200_dist_phase_ms(self.h, i) for i, k in enumerate(("gram", "factor", "solve"))}
 
     def counters(self):
-        return {k: self.lib.gprb200_dist_counter(self.h, i) for i, k in enumerate(("collectives", "bytes", "gemm_flops", "launches"))}
+        return {k: self.lib.gprb200_dist_counter(self.h, i) for i, k in enumerate(("collectives", "bytes", "gemm_flops", "launches", "stall_ms", "busy_ms", "update_flops"))}
 
     def close(self):
         if self.h:

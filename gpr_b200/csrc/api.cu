@@ -853,6 +853,21 @@ int gprb200_gemm_dev(gprb200_handle h, int form, int64_t M, int64_t N, int64_t K
     return gemm(c, (GemmForm)form, g);
 }
 
+int gprb200_gemm_stair_dev(gprb200_handle h, int64_t M, int64_t N, int64_t K, double alpha, const double* dA, int64_t lda,
+                           const double* dB, int64_t ldb, double beta, double* dC, int64_t ldc, const int* dStair, int64_t row0) {
+    if (!h) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, M >= 0 && N >= 0 && K >= 0 && M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31) && row0 >= 0 &&
+                          row0 + M < (1ll << 31), "gemm_stair_dev: bad extents"));
+    GP_TRY(require(c, dStair != nullptr, "gemm_stair_dev: null stair table (use gprb200_gemm_dev for a full C)"));
+    GemmArgs g{};
+    g.A = dA; g.lda = lda; g.B = dB; g.ldb = ldb; g.C = dC; g.ldc = ldc;
+    g.M = (int)M; g.N = (int)N; g.K = (int)K; g.alpha = alpha; g.beta = beta;
+    g.stair = dStair; g.stair_row0 = (int)row0;
+    return gemm(c, GEMM_NT, g);
+}
+
 int gprb200_gram_block_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_t col0, int64_t ncols, double* dOut,
                            int64_t ldo) {
     if (!h || !dOut) return -2;

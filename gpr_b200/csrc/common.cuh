@@ -39,6 +39,11 @@ struct GemmArgs {
     //      is global column (tri_first + (n / tri_cb) * tri_stride) * tri_cb + n % tri_cb, and B[k][n] = 0 for k < that
     int ktri;
     int tri_cb, tri_first, tri_stride;
+    // stair (device, may be null): "staircase" C, the trailing update of a block-cyclic Cholesky in ONE launch. Entry u is
+    // the first row (in the caller's row numbering) that columns [64 u, 64 u + 64) of C need; row r of C carries the
+    // number stair_row0 + r. A tile whose rows all lie before the stair of all of its columns exits at once.
+    const int* stair;
+    int stair_row0;
 };
 
 enum GemmForm { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };

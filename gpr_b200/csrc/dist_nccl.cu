@@ -6,14 +6,17 @@
 // as the torch.distributed form and as the one the CPU gloo tests exercise). What it reproduces of the reference:
 // the result of InvertKernelMatrix + C * Y (lib/GaussianProcess.cpp:531-560, :642-672).
 //
-// Layout. Block (i, j), i >= j, of nb x nb lives on rank (i mod Pr) * Pc + (j mod Pc). A rank stores each owned block
-// column j as ONE stacked panel: its owned block rows i >= j on top of each other (leading dimension even). Per step k:
+// Layout. Block (i, j), i >= j, of nb x nb lives on rank (i mod Pr) * Pc + (j mod Pc). A rank keeps ONE local matrix: its
+// owned block rows stacked (H rows) by its owned block columns side by side (Wtot columns); block column j uses the rows
+// from its first owned block row i >= j on (the part above is never touched: twice the memory of a packed lower
+// triangle, which buys a trailing update that is ONE tensor-core launch per step - gprb200_gemm_stair_dev - instead of
+// one per owned block column, whose partial last waves added up to several per cent). Per step k:
 //   grid column k mod Pc, panel stream: L_kk on the diagonal owner, W = inv(L_kk) broadcast down the column, each rank
 //     solves its rows X_i = A_ik W^T with one tensor-core GEMM;
 //   everybody, panel stream: X rows broadcast along the grid rows; the blocks that are a column operand L_jk broadcast
 //     down the grid columns (Pr roots, one NCCL group);
-//   everybody, main stream: A_ij -= X_i L_jk^T, one GEMM per owned block column; block column k + 1 is updated and
-//     factored first, on the panel stream (look-ahead), so its broadcasts overlap the trailing update.
+//   everybody, main stream: A_ij -= X_i L_jk^T for all owned block columns j > k in one staircase GEMM; block column
+//     k + 1 is updated and factored first, on the panel stream (look-ahead), so its broadcasts overlap the update.
 // INFO is a device int for the whole factorisation, agreed on by one all-reduce(min) at the end.
 #include <cuda_runtime.h>
 #include <nccl.h>
@@ -33,11 +36,18 @@ thread_local std::string g_create_error;
 
 struct Problem {
     int64_t N = 0, nb = 0, nblk = 0, H = 0;
+    int dim = 0;
+    double* dX = nullptr;                    // training inputs (N x dim)
     std::vector<int64_t> hgt, roff;          // block heights; offset of block row i in a stacked panel (-1: not mine)
     std::vector<int64_t> myrows, mine;       // owned block rows / block columns
-    std::vector<double*> cols, invl;         // per block column: stacked panel, inverted diagonal blocks (owner only)
-    std::vector<int64_t> ld, off;            // leading dimension and first stacked row (offset of first i >= j)
+    double* A = nullptr;                     // the local matrix, H x Wtot (ld LDA)
+    int64_t LDA = 0, Wtot = 0;
+    std::vector<int64_t> coff;               // local column offset of owned block column j (-1: not mine)
+    std::vector<double*> cols, invl;         // per block column: view into A from its first row on; inverted diagonal blocks
+    std::vector<int64_t> ld, off;            // leading dimension (LDA) and first stacked row (offset of first i >= j)
     std::vector<int64_t> first;              // first owned block row >= j (-1: none)
+    int* stair = nullptr;                    // per 64 local columns: first local row they need (gprb200_gemm_stair_dev)
+    double* Bop[2] = {nullptr, nullptr};     // column operands L_jk of step k for the owned j > k, in local column order
     double* row[2] = {nullptr, nullptr};     // solved panel rows of step k (H x nb)
     double* W[2] = {nullptr, nullptr};       // inv(L_kk)
     double* eye = nullptr;
@@ -46,7 +56,7 @@ struct Problem {
     long long* dflag = nullptr;
     double* dsum = nullptr;
     std::vector<void*> allocs;
-    std::vector<cudaEvent_t> ev_main, ev_panel;
+    std::vector<cudaEvent_t> ev_main, ev_panel, ev_start;
     bool factored = false;
     double logdet = 0.0;
 };
@@ -64,6 +74,9 @@ struct gprb200_dist {
     Problem P;
     double ms[3] = {0, 0, 0};
     double n_coll = 0, n_bytes = 0, n_flop = 0, launches0 = 0, n_launch = 0;
+    int profile = 0;                         // option "profile": timed per-step events on the main stream
+    double n_flop_main = 0;                  // flop of the main-stream trailing updates (last learn)
+    double stall_ms = 0, busy_ms = 0;        // main stream: waiting for a panel / inside trailing updates (last learn)
 };
 
 namespace {
@@ -100,6 +113,13 @@ __global__ void sub_kernel(double* __restrict__ out, const double* __restrict__ 
     if (i < n) out[i] = a[i] - b[i];
 }
 
+// rows of M doubles <-> rows of ld doubles (right-hand sides are kept with an even leading dimension)
+__global__ void repitch_kernel(double* __restrict__ dst, int64_t ldd, const double* __restrict__ src, int64_t lds, int64_t rows,
+                               int64_t M) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < rows * M) dst[(i / M) * ldd + i % M] = src[(i / M) * lds + i % M];
+}
+
 __global__ void eye_kernel(double* __restrict__ out, int64_t n) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i < n * n) out[i] = (i / n == i % n) ? 1.0 : 0.0;
@@ -117,6 +137,7 @@ int release_problem(gprb200_dist* d) {
     for (void* p : P.allocs) cudaFree(p);
     for (cudaEvent_t e : P.ev_main) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : P.ev_panel) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : P.ev_start) if (e) cudaEventDestroy(e);
     P = Problem();
     return 0;
 }
@@ -142,26 +163,41 @@ inline int bcast(gprb200_dist* d, double* buf, int64_t count, int root, ncclComm
 namespace {
 
 // ---- ownership maps and device buffers ----------------------------------------------------------------------------
-int setup_problem(gprb200_dist* d, int64_t N, int64_t nb) {
+int setup_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb) {
+    if (d->P.N == N && d->P.nb == nb && d->P.dim == dim && d->P.dX) {   // same shape as the last learn: keep the buffers
+        d->P.factored = false;
+        return 0;
+    }
     release_problem(d);
     Problem& P = d->P;
-    P.N = N; P.nb = nb; P.nblk = (N + nb - 1) / nb;
+    P.N = N; P.nb = nb; P.dim = dim; P.nblk = (N + nb - 1) / nb;
     P.hgt.resize(P.nblk); P.roff.assign(P.nblk, -1);
     for (int64_t i = 0; i < P.nblk; ++i) P.hgt[i] = std::min(nb, N - i * nb);
     for (int64_t i = d->pr; i < P.nblk; i += d->Pr) { P.roff[i] = P.H; P.H += P.hgt[i]; P.myrows.push_back(i); }
     for (int64_t j = d->pc; j < P.nblk; j += d->Pc) P.mine.push_back(j);
     P.cols.assign(P.nblk, nullptr); P.invl.assign(P.nblk, nullptr);
     P.ld.assign(P.nblk, 0); P.off.assign(P.nblk, 0); P.first.assign(P.nblk, -1);
+    P.coff.assign(P.nblk, -1);
+    for (int64_t j : P.mine) { P.coff[j] = P.Wtot; P.Wtot += P.hgt[j]; }
+    P.LDA = (P.Wtot + 1) / 2 * 2;
+    RK(dmalloc(d, (void**)&P.A, (size_t)std::max<int64_t>(P.H, 1) * std::max<int64_t>(P.LDA, 2) * 8));
+    std::vector<int> stair((size_t)(P.Wtot + 63) / 64 + 1, (int)P.H);
     for (int64_t j : P.mine) {
         int64_t off, first;
         first_at_or_after(d, j, &off, &first);
         P.off[j] = off; P.first[j] = first;
         if (first < 0) continue;
-        P.ld[j] = (P.hgt[j] + 1) / 2 * 2;
-        RK(dmalloc(d, (void**)&P.cols[j], (size_t)(P.H - off) * P.ld[j] * 8));
+        P.ld[j] = P.LDA;
+        P.cols[j] = P.A + off * P.LDA + P.coff[j];
+        // columns [c, c + 64) of the diagonal block need the rows from c on (lower triangle), the others the whole block row
+        for (int64_t c = 0; c < P.hgt[j]; c += 64) stair[(size_t)(P.coff[j] + c) / 64] = (int)(off + (first == j ? c : 0));
         if (first == j) RK(dmalloc(d, (void**)&P.invl[j], (size_t)((P.hgt[j] + 127) / 128) * 128 * 128 * 8));
     }
+    RK(dmalloc(d, (void**)&P.stair, stair.size() * sizeof(int)));
+    CK(cudaMemcpyAsync(P.stair, stair.data(), stair.size() * sizeof(int), cudaMemcpyHostToDevice, d->sm));
+    CK(cudaStreamSynchronize(d->sm));   // `stair` is a local
     for (int s = 0; s < 2; ++s) {
+        RK(dmalloc(d, (void**)&P.Bop[s], (size_t)std::max<int64_t>(P.Wtot, 1) * nb * 8));
         RK(dmalloc(d, (void**)&P.row[s], (size_t)std::max<int64_t>(P.H, 1) * nb * 8));
         RK(dmalloc(d, (void**)&P.W[s], (size_t)nb * nb * 8));
         if (d->Pr > 1) {
@@ -174,15 +210,18 @@ int setup_problem(gprb200_dist* d, int64_t N, int64_t nb) {
         }
     }
     RK(dmalloc(d, (void**)&P.eye, (size_t)nb * nb * 8));
+    RK(dmalloc(d, (void**)&P.dX, (size_t)N * dim * 8));
     RK(dmalloc(d, (void**)&P.dinfo, 256));
     RK(dmalloc(d, (void**)&P.dflag, 256));
     RK(dmalloc(d, (void**)&P.dsum, 256));
     eye_kernel<<<(unsigned)((nb * nb + 255) / 256), 256, 0, d->sm>>>(P.eye, nb);
     CK(cudaGetLastError());
     P.ev_main.assign(P.nblk, nullptr); P.ev_panel.assign(P.nblk, nullptr);
+    if (d->profile) P.ev_start.assign(P.nblk, nullptr);
     for (int64_t k = 0; k < P.nblk; ++k) {
-        CK(cudaEventCreateWithFlags(&P.ev_main[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&P.ev_main[k], d->profile ? cudaEventDefault : cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&P.ev_panel[k], cudaEventDisableTiming));
+        if (d->profile) CK(cudaEventCreate(&P.ev_start[k]));
     }
     return 0;
 }
@@ -234,7 +273,8 @@ int panel_factor(gprb200_dist* d, int64_t k) {
     return 0;
 }
 
-// All ranks, panel stream: the solved panel rows along the grid rows, then the column operands down the grid columns.
+// All ranks, panel stream: the solved panel rows along the grid rows, then the column operands L_jk of the owned block
+// columns j > k down the grid columns, left in Bop[k % 2] in local column order (the B operand of the staircase update).
 int distribute(gprb200_dist* d, int64_t k) {
     Problem& P = d->P;
     if (k == P.nblk - 1) return 0;
@@ -243,48 +283,66 @@ int distribute(gprb200_dist* d, int64_t k) {
     first_at_or_after(d, k + 1, &o1, &first);
     double* X = P.row[k % 2];
     if (d->Pc > 1 && first >= 0) RK(bcast(d, X, (P.H - o1) * nb, (int)(k % d->Pc), d->row_comm, d->sp));
-    if (d->Pr > 1) {
-        std::vector<int64_t> total(d->Pr, 0);
-        for (int64_t j : P.mine) {
-            if (j <= k) continue;
-            const int r2 = (int)(j % d->Pr);
-            if (r2 == d->pr)    // this rank holds those block rows in X: pack them
-                CK(cudaMemcpyAsync(P.colbuf[k % 2][r2] + total[r2] * nb, X + (P.roff[j] - o1) * nb, (size_t)P.hgt[j] * nb * 8,
-                                   cudaMemcpyDeviceToDevice, d->sp));
-            total[r2] += P.hgt[j];
-        }
-        NK(ncclGroupStart());
-        for (int r2 = 0; r2 < d->Pr; ++r2)
-            if (total[r2] > 0) RK(bcast(d, P.colbuf[k % 2][r2], total[r2] * nb, r2, d->col_comm, d->sp));
-        NK(ncclGroupEnd());
+    double* B = P.Bop[k % 2];
+    auto jbeg = std::upper_bound(P.mine.begin(), P.mine.end(), k);
+    if (jbeg == P.mine.end()) return 0;
+    const int64_t c0 = P.coff[*jbeg];                  // B row of block j: coff[j] - c0
+    auto copy_block = [&](double* dst, const double* src, int64_t rows) -> int {
+        CK(cudaMemcpyAsync(dst, src, (size_t)rows * nb * 8, cudaMemcpyDeviceToDevice, d->sp));
+        return 0;
+    };
+    if (d->Pr == 1) {   // this rank holds every block row of X: pick the owned ones
+        for (auto it = jbeg; it != P.mine.end(); ++it)
+            RK(copy_block(B + (P.coff[*it] - c0) * nb, X + (P.roff[*it] - o1) * nb, P.hgt[*it]));
+        return 0;
+    }
+    std::vector<int64_t> total(d->Pr, 0);
+    int groups = 0;
+    for (auto it = jbeg; it != P.mine.end(); ++it) total[*it % d->Pr] += P.hgt[*it];
+    for (int r2 = 0; r2 < d->Pr; ++r2) groups += total[r2] > 0;
+    if (groups == 1) {  // (Pc a multiple of Pr: all owned block columns meet the same grid row) straight into B
+        const int r2 = (int)(*jbeg % d->Pr);
+        if (r2 == d->pr)
+            for (auto it = jbeg; it != P.mine.end(); ++it)
+                RK(copy_block(B + (P.coff[*it] - c0) * nb, X + (P.roff[*it] - o1) * nb, P.hgt[*it]));
+        return bcast(d, B, total[r2] * nb, r2, d->col_comm, d->sp);
+    }
+    std::vector<int64_t> pos(d->Pr, 0);
+    for (auto it = jbeg; it != P.mine.end(); ++it) {
+        const int r2 = (int)(*it % d->Pr);
+        if (r2 == d->pr) RK(copy_block(P.colbuf[k % 2][r2] + pos[r2] * nb, X + (P.roff[*it] - o1) * nb, P.hgt[*it]));
+        pos[r2] += P.hgt[*it];
+    }
+    NK(ncclGroupStart());
+    for (int r2 = 0; r2 < d->Pr; ++r2)
+        if (total[r2] > 0) RK(bcast(d, P.colbuf[k % 2][r2], total[r2] * nb, r2, d->col_comm, d->sp));
+    NK(ncclGroupEnd());
+    std::fill(pos.begin(), pos.end(), 0);
+    for (auto it = jbeg; it != P.mine.end(); ++it) {
+        const int r2 = (int)(*it % d->Pr);
+        RK(copy_block(B + (P.coff[*it] - c0) * nb, P.colbuf[k % 2][r2] + pos[r2] * nb, P.hgt[*it]));
+        pos[r2] += P.hgt[*it];
     }
     return 0;
 }
 
-// L_jk (hgt[j] x nb) as received at step k
-const double* col_operand(gprb200_dist* d, int64_t j, int64_t k) {
+// A_ij -= X_i L_jk^T for the owned block columns jfrom <= j <= jto (consecutive in `mine`), all their rows, ONE launch
+int update(gprb200_dist* d, int64_t k, int64_t jfrom, int64_t jto, gprb200_handle h) {
     Problem& P = d->P;
-    if (d->Pr == 1) {
-        int64_t o1, first;
-        first_at_or_after(d, k + 1, &o1, &first);
-        return P.row[k % 2] + (P.roff[j] - o1) * P.nb;
-    }
-    const int r2 = (int)(j % d->Pr);
-    int64_t pos = 0;
-    for (int64_t q : P.mine) if (q > k && q < j && q % d->Pr == r2) pos += P.hgt[q];
-    return P.colbuf[k % 2][r2] + pos * P.nb;
-}
-
-// Owned blocks of block column j: A_ij -= X_i L_jk^T, i >= j (one GEMM, K = nb)
-int update(gprb200_dist* d, int64_t j, int64_t k, gprb200_handle h) {
-    Problem& P = d->P;
-    if (!P.cols[j]) return 0;
+    if (P.first[jfrom] < 0) return 0;                   // no owned rows at or below the first (hence any) of these columns
     int64_t o1, f1;
     first_at_or_after(d, k + 1, &o1, &f1);
-    const int64_t rows = P.H - P.off[j];
-    const double* X = P.row[k % 2] + (P.off[j] - o1) * P.nb;
-    GK(h, gprb200_gemm_dev(h, 0, rows, P.hgt[j], P.nb, -1.0, X, P.nb, col_operand(d, j, k), P.nb, 1.0, P.cols[j], P.ld[j], 0));
-    d->n_flop += 2.0 * rows * P.hgt[j] * P.nb;
+    const int64_t c0 = P.coff[*std::upper_bound(P.mine.begin(), P.mine.end(), k)];
+    const int64_t oS = P.off[jfrom], rows = P.H - oS, ncols = P.coff[jto] + P.hgt[jto] - P.coff[jfrom];
+    GK(h, gprb200_gemm_stair_dev(h, rows, ncols, P.nb, -1.0, P.row[k % 2] + (oS - o1) * P.nb, P.nb,
+                                 P.Bop[k % 2] + (P.coff[jfrom] - c0) * P.nb, P.nb, 1.0, P.A + oS * P.LDA + P.coff[jfrom], P.LDA,
+                                 P.stair + P.coff[jfrom] / 64, oS));
+    for (auto it = std::lower_bound(P.mine.begin(), P.mine.end(), jfrom); it != P.mine.end() && *it <= jto; ++it)
+        if (P.first[*it] >= 0) {
+            const double f = 2.0 * (P.H - P.off[*it]) * P.hgt[*it] * P.nb;
+            d->n_flop += f;
+            if (h == d->hm) d->n_flop_main += f;
+        }
     return 0;
 }
 
@@ -303,18 +361,31 @@ int factor(gprb200_dist* d, int* info_out) {
             // look-ahead: block column k + 1 gets this panel first, off the main stream, and is factored at once so
             // that its broadcasts overlap everybody's trailing update
             if (k >= 1) CK(cudaStreamWaitEvent(d->sp, P.ev_main[k - 1], 0));
-            RK(update(d, k + 1, k, d->hp));
+            RK(update(d, k, k + 1, k + 1, d->hp));
             RK(panel_factor(d, k + 1));
         }
         CK(cudaStreamWaitEvent(d->sm, P.ev_panel[k], 0));
-        for (int64_t j : P.mine)
-            if (j > k + 1 || (j == k + 1 && !nxt_mine)) RK(update(d, j, k, d->hm));
+        if (!P.ev_start.empty()) CK(cudaEventRecord(P.ev_start[k], d->sm));
+        {
+            auto it = std::upper_bound(P.mine.begin(), P.mine.end(), nxt_mine ? k + 1 : k);
+            if (it != P.mine.end()) RK(update(d, k, *it, P.mine.back(), d->hm));
+        }
         CK(cudaEventRecord(P.ev_main[k], d->sm));
     }
     // A rank that meets a non-SPD block keeps following the schedule (nobody hangs in a broadcast); all ranks agree on
     // INFO here: the smallest failing leading minor.
     CK(cudaStreamSynchronize(d->sp));
     CK(cudaStreamSynchronize(d->sm));
+    if (!P.ev_start.empty()) {   // where the main stream's time went: inside updates, or waiting for the panel of the step
+        d->stall_ms = d->busy_ms = 0.0;
+        for (int64_t k = 0; k < nblk; ++k) {
+            float a = 0.f, b = 0.f;
+            CK(cudaEventElapsedTime(&a, P.ev_start[k], P.ev_main[k]));
+            if (k > 0) CK(cudaEventElapsedTime(&b, P.ev_main[k - 1], P.ev_start[k]));
+            else CK(cudaEventElapsedTime(&b, d->t1, P.ev_start[0]));
+            d->busy_ms += a; d->stall_ms += b;
+        }
+    }
     int info = 0;
     CK(cudaMemcpy(&info, P.dinfo, sizeof(int), cudaMemcpyDeviceToHost));
     const long long big = 1LL << 62;
@@ -383,14 +454,21 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
     std::vector<int64_t> zoff(nblk, -1);
     for (int64_t k = 0; k < nblk; ++k)
         if (k % d->Pr == d->pr && k % d->Pc == d->pc) { zoff[k] = ndiag; ndiag += P.hgt[k]; }
-    if ((rc = talloc(&y, (size_t)N * ld)) || (rc = talloc(&out, (size_t)N * ld)) ||
+    double* stage = nullptr;     // contiguous N x M image of the host array (a pitched copy of 8-byte rows crawls)
+    if ((rc = talloc(&y, (size_t)N * ld)) || (rc = talloc(&out, (size_t)N * ld)) || (rc = talloc(&stage, (size_t)N * M)) ||
         (rc = talloc(&acc, (size_t)std::max<int64_t>(P.H, 1) * ld)) || (rc = talloc(&msg[0], (size_t)nb * ld)) ||
         (rc = talloc(&msg[1], (size_t)nb * ld)) || (rc = talloc(&zown, (size_t)std::max<int64_t>(ndiag, 1) * ld))) {
         tfree();
         return rc;
     }
     auto body = [&]() -> int {
-        CK(cudaMemcpy2DAsync(y, (size_t)ld * 8, Yhost, (size_t)M * 8, (size_t)M * 8, (size_t)N, cudaMemcpyHostToDevice, st));
+        if (ld == M) {
+            CK(cudaMemcpyAsync(y, Yhost, (size_t)N * M * 8, cudaMemcpyHostToDevice, st));
+        } else {
+            CK(cudaMemcpyAsync(stage, Yhost, (size_t)N * M * 8, cudaMemcpyHostToDevice, st));
+            repitch_kernel<<<(unsigned)((N * M + 255) / 256), 256, 0, st>>>(y, ld, stage, M, N, M);
+            CK(cudaGetLastError());
+        }
         // ---- forward
         for (int64_t k = 0; k < nblk; ++k) {
             const int64_t w = P.hgt[k];
@@ -456,8 +534,15 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
             CK(cudaMemcpyAsync(out, acc, (size_t)N * ld * 8, cudaMemcpyDeviceToDevice, st));   // Pr = 1: every rank's acc already is the whole x
         }
         CK(cudaEventRecord(d->t3, st));
-        if (alpha_host)
-            CK(cudaMemcpy2DAsync(alpha_host, (size_t)M * 8, out, (size_t)ld * 8, (size_t)M * 8, (size_t)N, cudaMemcpyDeviceToHost, st));
+        if (alpha_host) {
+            const double* src = out;
+            if (ld != M) {
+                repitch_kernel<<<(unsigned)((N * M + 255) / 256), 256, 0, st>>>(stage, M, out, ld, N, M);
+                CK(cudaGetLastError());
+                src = stage;
+            }
+            CK(cudaMemcpyAsync(alpha_host, src, (size_t)N * M * 8, cudaMemcpyDeviceToHost, st));
+        }
         CK(cudaStreamSynchronize(st));
         return 0;
     };
@@ -564,6 +649,11 @@ int gprb200_dist_set_kernel(gprb200_dist_handle d, const int32_t* ops, int nops,
 
 int gprb200_dist_set_option(gprb200_dist_handle d, const char* name, int64_t value) {
     if (!d) return -2;
+    if (name && std::strcmp(name, "profile") == 0) {    // local: timed per-step events (takes effect at the next allocation)
+        d->profile = value != 0;
+        release_problem(d);
+        return 0;
+    }
     GK(d->hm, gprb200_set_option(d->hm, name, value));
     GK(d->hp, gprb200_set_option(d->hp, name, value));
     return 0;
@@ -578,13 +668,11 @@ int gprb200_dist_learn(gprb200_dist_handle d, const double* X, int64_t N, int di
     if (nb == 0) nb = 1024;
     if (nb < 128 || nb % 128 != 0) return fail(d, -2, "gprb200_dist_learn: nb must be a multiple of 128 (the Cholesky diagonal block)");
     CK(cudaSetDevice(d->dev));
-    d->n_coll = d->n_bytes = d->n_flop = 0.0;
+    d->n_coll = d->n_bytes = d->n_flop = d->n_flop_main = 0.0;
     const double l0 = (double)gprb200_launch_count(d->hm) + (double)gprb200_launch_count(d->hp);
-    RK(setup_problem(d, N, nb));
-    double* dX = nullptr;
-    RK(dmalloc(d, (void**)&dX, (size_t)N * dim * 8));
-    CK(cudaMemcpyAsync(dX, X, (size_t)N * dim * 8, cudaMemcpyHostToDevice, d->sm));
-    GK(d->hm, gprb200_set_train_dev(d->hm, dX, N, dim, nullptr, 0, sigma));
+    RK(setup_problem(d, N, dim, nb));
+    CK(cudaMemcpyAsync(d->P.dX, X, (size_t)N * dim * 8, cudaMemcpyHostToDevice, d->sm));
+    GK(d->hm, gprb200_set_train_dev(d->hm, d->P.dX, N, dim, nullptr, 0, sigma));
     CK(cudaEventRecord(d->t0, d->sm));
     RK(build_gram(d));
     CK(cudaEventRecord(d->t1, d->sm));
@@ -634,6 +722,9 @@ double gprb200_dist_counter(gprb200_dist_handle d, int which) {
         case 1: return d->n_bytes;
         case 2: return d->n_flop;
         case 3: return d->n_launch;
+        case 4: return d->stall_ms;
+        case 5: return d->busy_ms;
+        case 6: return d->n_flop_main;
     }
     return -1.0;
 }

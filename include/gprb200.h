@@ -166,6 +166,15 @@ int gprb200_lu_inverse(gprb200_handle h, const double* A, int64_t n, double* Ain
 int gprb200_gemm_dev(gprb200_handle h, int form, int64_t M, int64_t N, int64_t K, double alpha, const double* dA,
                      int64_t lda, const double* dB, int64_t ldb, double beta, double* dC, int64_t ldc, int lower);
 
+/* C = alpha A B^T + beta C (NT form as above) for a "staircase" C: the trailing update of a block-cyclic Cholesky,
+ * where a rank's owned block columns start at different rows, in ONE launch instead of one per block column (whose
+ * partial last waves add up). dStair (DEVICE ints, one per 64 columns of C): the first row, in the caller's own row
+ * numbering, that those columns need; row r of C has the number row0 + r. 128-row tiles lying entirely before the stair of
+ * all their columns are skipped, everything else is computed in full (so entries above a column's stair may or may not be
+ * updated: the caller must not care). Part of the dpotrf that replaces lib/GaussianProcess.cpp:531-560 at large N. */
+int gprb200_gemm_stair_dev(gprb200_handle h, int64_t M, int64_t N, int64_t K, double alpha, const double* dA, int64_t lda,
+                           const double* dB, int64_t ldb, double beta, double* dC, int64_t ldc, const int* dStair, int64_t row0);
+
 /* Block [row0, row0+nrows) x [col0, col0+ncols) of K + sigma^2 I over the training samples (ComputeKernelMatrix +
  * AddNoiseToKernelMatrix, lib/GaussianProcess.cpp:363-402, :375-381), written to a device buffer: lets every rank of
  * a multi-GPU factorisation build exactly the block columns it owns, with no exchange. */

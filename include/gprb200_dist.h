@@ -38,14 +38,16 @@ const char* gprb200_dist_last_error(gprb200_dist_handle d); /* d may be NULL: la
 
 /* The kernel in the op-code form of gprb200_set_kernel (gprb200.h; KernelFactory::GetKernel, include/KernelFactory.h). */
 int gprb200_dist_set_kernel(gprb200_dist_handle d, const int32_t* ops, int nops, const double* params, int nparams);
-/* Options of the LOCAL single-GPU library handles (gprb200_set_option names, e.g. "gemm_small"), both streams. */
+/* Options of the LOCAL single-GPU library handles (gprb200_set_option names, e.g. "gemm_small"), both streams; and
+ * "profile" (0 / 1): timed events around every trailing update, for counters 4 and 5 below. */
 int gprb200_dist_set_option(gprb200_dist_handle d, const char* name, int64_t value);
 
 /* Learn: X is N x dim, Y is N x M (row-major HOST arrays, the same on every rank; M small - many outputs shard by
  * column instead, see gpr_b200.dist.ShardedOutputsGP). nb = block size, a multiple of 128 (0: 1024).
  * On return every rank has alpha (N x M, host) and *logdet. alpha / logdet may be NULL (factorisation only).
  * Device memory: the owned blocks of the lower triangle (about 4 N^2 / world bytes) stay allocated until the next
- * learn / destroy so that gprb200_dist_solve can reuse the factor. */
+ * learn / destroy so that gprb200_dist_solve can reuse the factor; a learn of the same (N, dim, nb) reuses them without
+ * any allocation. */
 int gprb200_dist_learn(gprb200_dist_handle d, const double* X, int64_t N, int dim, const double* Y, int64_t M,
                        double sigma, int64_t nb, double* alpha, double* logdet);
 /* Another right-hand side against the factor of the last learn (collective). */
@@ -55,7 +57,8 @@ int gprb200_dist_solve(gprb200_dist_handle d, const double* Y, int64_t M, double
  * which = 0 Gram blocks, 1 factorisation, 2 solve. Take the max over ranks for a job time. */
 double gprb200_dist_phase_ms(gprb200_dist_handle d, int which);
 /* Counters of the last learn on this rank: 0 NCCL calls issued, 1 bytes broadcast / reduced, 2 GEMM flop issued,
- * 3 kernels launched through libgprb200.so. */
+ * 3 kernels launched through libgprb200.so; with option "profile": 4 ms the main stream waited for a panel, 5 ms it spent
+ * inside trailing updates, 6 the flop of those updates (factorisation only). */
 double gprb200_dist_counter(gprb200_dist_handle d, int which);
 
 #ifdef __cplusplus

@@ -31,6 +31,11 @@ def main():
     ops_, params = gpr_b200.KernelFactory.GetKernel(KS).lower()
     d = capi_dist.DistHandle(local, rank, world, uid, grid)
     d.set_kernel(ops_, params)
+    if os.environ.get("DIST_PROFILE"):
+        d.set_option("profile", 1)
+    for kv in os.environ.get("DIST_OPTS", "").split(","):
+        if "=" in kv:
+            d.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     out = {}
     for it in range(reps):
         if world > 1:
@@ -39,13 +44,15 @@ def main():
         alpha, logdet = d.learn(X, Y, 1.0, nb=nb)
         wall = time.perf_counter() - t0
         ph = d.phase_ms()
-        tm = torch.tensor([ph["gram"], ph["factor"], ph["solve"], wall * 1e3], dtype=torch.float64)
+        tm = torch.tensor([ph["gram"], ph["factor"], ph["solve"], wall * 1e3, d.counters()["stall_ms"]], dtype=torch.float64)
         if world > 1:
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         c = d.counters()
+        stall = tm[4].item()
         out = {"N": N, "nb": nb, "world": world, "grid": sys.argv[3] if grid else "default", "impl": "libgprb200_dist.so (NCCL from C++)",
                "gram_s": tm[0].item() * 1e-3, "factor_s": tm[1].item() * 1e-3, "solve_s": tm[2].item() * 1e-3,
                "learn_wall_s_host_to_host": tm[3].item() * 1e-3, "factor_TFs_total": N ** 3 / 3.0 / (tm[1].item() * 1e-3) * 1e-12,
+               "stall_ms_max_over_ranks": stall, "busy_ms": c["busy_ms"], "gemm_TFs_inside_updates_this_rank": (c["update_flops"] / c["busy_ms"] * 1e-9 if c["busy_ms"] > 0 else None),
                "collectives": c["collectives"], "exchanged_GB": c["bytes"] * 1e-9, "launches": c["launches"], "logdet": logdet}
     if world > 1:
         chk = torch.from_numpy(alpha.copy())
