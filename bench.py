@@ -449,8 +449,9 @@ def headline_c5(args, env, detail):
         # the whole schedule under the C-ABI (libgprb200_dist.so, NCCL from C++): every step takes HOST X, Y and returns a
         # HOST alpha, so one loop gives both the device-timed value (the library's CUDA events) and the end-to-end time
         from gpr_b200 import capi_dist
-        dh = capi_dist.DistHandle(local_rank, rank, world, capi_dist.exchange_id(), grid)
+        dh = capi_dist.DistHandle(local_rank, rank, world, capi_dist.exchange_id(), grid if args.grid else None)
         dh.set_kernel(ops_, params)
+        grid = (int(dh.counters()["Pr"]), int(dh.counters()["Pc"]))
         dh.learn(X[:8192], Y[:8192], C3_SIGMA, nb=nb)          # communicators, kernel attributes
         for _ in range(1 if args.large_quick_warmup else args.warmup):
             dh.learn(X, Y, C3_SIGMA, nb=nb)
@@ -547,7 +548,8 @@ def headline_c5(args, env, detail):
                         "Sum(Sum(Gaussian,Periodic),White), d=8, M=1, fp64",
             "N": N, "d": C3_D, "M": M, "nb": nb, "grid": "%dx%d" % grid,
             "layout": "2-D block-cyclic %d x %d, lower triangle only, %.1f GB per GPU" % (grid[0], grid[1], 4.0 * N * N / world * 1e-9),
-            "parallelism": "Pr x Pc block-cyclic Cholesky, NCCL broadcasts on row / column communicators, one-panel look-ahead",
+            "parallelism": "Pr x Pc block-cyclic Cholesky (row map mirrored), NCCL broadcasts on row / column communicators, "
+                           "one-panel look-ahead, one staircase GEMM per trailing update",
             "useful_flops": flops, "l2": "inputs larger than L2 (%.0f GB per GPU)" % (4.0 * N * N / world * 1e-9),
             "learn_s": total_ms * 1e-3, "gram_s": gram_ms * 1e-3, "cholesky_s": factor_ms * 1e-3, "solve_s": solve_ms * 1e-3,
             "cholesky_tflops_total": chol_tf, "cholesky_frac_of_peak": chol_tf / (FP64_PEAK_TFLOPS * world),

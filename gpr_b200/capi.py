@@ -49,6 +49,7 @@ _PROTOS = {
     "gprb200_gemm_stair_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_void_p, C.c_int64, C.c_void_p,
                                          C.c_int64, C.c_double, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
     "gprb200_gram_block_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64]),
+    "gprb200_gram_pair_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
     "gprb200_potrf_panel_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
                                           C.POINTER(C.c_int)]),
     "gprb200_potrf_panel_async_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,

@@ -37,6 +37,12 @@ def load_dist_library():
     if _lib is not None:
         return _lib
     load_library()
+    # libgprb200_dist.so needs "libnccl.so.2". torch ships its own (newer) one under the same soname: whichever is mapped
+    # first serves both, and torch does not import against the older system library - so let torch map its copy first.
+    try:
+        import torch  # noqa: F401
+    except ImportError:
+        pass
     if not os.path.exists(DIST_LIB_PATH):
         raise ImportError(f"{DIST_LIB_PATH} not found: build it with `make -C gpr_b200/csrc` (needs nccl.h / libnccl)")
     lib = C.CDLL(DIST_LIB_PATH, mode=C.RTLD_GLOBAL)
@@ -71,7 +77,7 @@ def _arr(a):
 
 
 class DistHandle:
-    """One rank of a Pr x Pc grid. grid=None: the library's default (8 -> 2 x 4)."""
+    """One rank of a Pr x Pc grid. grid=None: the library's default (8 -> 4 x 2)."""
 
     def __init__(self, device, rank=0, world=1, unique_id=None, grid=None):
         self.lib = load_dist_library()
@@ -126,7 +132,7 @@ class DistHandle:
         return {k: self.lib.gprb200_dist_phase_ms(self.h, i) for i, k in enumerate(("gram", "factor", "solve"))}
 
     def counters(self):
-        return {k: self.lib.gprb200_dist_counter(self.h, i) for i, k in enumerate(("collectives", "bytes", "gemm_flops", "launches", "stall_ms", "busy_ms", "update_flops"))}
+        return {k: self.lib.gprb200_dist_counter(self.h, i) for i, k in enumerate(("collectives", "bytes", "gemm_flops", "launches", "stall_ms", "busy_ms", "update_flops", "Pr", "Pc"))}
 
     def close(self):
         if self.h:

@@ -845,11 +845,16 @@ int gprb200_gemm_dev(gprb200_handle h, int form, int64_t M, int64_t N, int64_t K
     if (!h) return -2;
     Ctx* c = h;
     GP_TRY(use_device(c));
-    GP_TRY(require(c, form >= 0 && form <= 2 && M >= 0 && N >= 0 && K >= 0 && M < (1ll << 31) && N < (1ll << 31) &&
+    GP_TRY(require(c, form >= 0 && form <= 3 && M >= 0 && N >= 0 && K >= 0 && M < (1ll << 31) && N < (1ll << 31) &&
                           K < (1ll << 31), "gemm_dev: bad form or extents"));
     GemmArgs g{};
     g.A = dA; g.lda = lda; g.B = dB; g.ldb = ldb; g.C = dC; g.ldc = ldc;
     g.M = (int)M; g.N = (int)N; g.K = (int)K; g.alpha = alpha; g.beta = beta; g.lower = lower ? 1 : 0;
+    if (form == 3) {    // NT with a lower-triangular B: the k loop of a tile stops at its last column
+        GP_TRY(require(c, !lower, "gemm_dev: form 3 has no lower-only variant"));
+        g.ktri = 4;
+        return gemm(c, GEMM_NT, g);
+    }
     return gemm(c, (GemmForm)form, g);
 }
 
@@ -883,6 +888,16 @@ int gprb200_gram_block_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_
     if (hi > lo && c->sigma != 0.0)
         GP_TRY(add_diag(c, dOut + (lo - row0) * ldo + (lo - col0), ldo, hi - lo, c->sigma * c->sigma));
     return 0;
+}
+
+int gprb200_gram_pair_dev(gprb200_handle h, const double* dXa, int64_t na, const double* dXb, int64_t nb, double* dOut,
+                          int64_t ldo) {
+    if (!h || !dOut || !dXa || !dXb) return -2;
+    Ctx* c = h;
+    GP_TRY(use_device(c));
+    GP_TRY(require(c, c->have_train && c->have_kernel, "gram_pair: need a kernel and samples (for the input dimension)"));
+    GP_TRY(require(c, na > 0 && nb > 0 && ldo >= nb, "gram_pair: bad extents"));
+    return gram_build(c, dXa, na, dXb, nb, dOut, ldo, false, false, 0.0);
 }
 
 int gprb200_potrf_panel_dev(gprb200_handle h, double* dP, int64_t ld, int64_t rows, int64_t w, double* dInvL, int* info) {

@@ -37,6 +37,8 @@ struct GemmArgs {
     //   2: A and B (K x M, K x N) are lower triangular            ->  k starts at max(first row, first column) (LAUUM, TN)
     //   3: as 1, but B's columns are a COMPACT selection of cyclic column blocks (trtri_cols, solve.cu): local column n
     //      is global column (tri_first + (n / tri_cb) * tri_stride) * tri_cb + n % tri_cb, and B[k][n] = 0 for k < that
+    //   4: NT form, B (N x K) is lower triangular, B[n][k] = 0 for k > n  ->  k ENDS after the tile's last column (the
+    //      product with an inverted Cholesky block: X = A inv(L)^T)
     int ktri;
     int tri_cb, tri_first, tri_stride;
     // stair (device, may be null): "staircase" C, the trailing update of a block-cyclic Cholesky in ONE launch. Entry u is

@@ -142,7 +142,7 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     if (!map_tile<BM, BN>(blockIdx.x, g.lower, tiles_m, tiles_n, ti, tj)) return;
     const int m0 = ti * BM, n0 = tj * BN;
     if (m0 >= g.M || n0 >= g.N) return;
-    if (EXT && g.stair != nullptr) {   // staircase C: nothing of this tile is below the stair of its columns
+    if (g.stair != nullptr) {   // staircase C: nothing of this tile is below the stair of its columns
         int first = g.stair[n0 >> 6];
         if (BN > 64 && n0 + 64 < g.N) first = min(first, g.stair[(n0 >> 6) + 1]);
         if (g.stair_row0 + m0 + BM <= first) return;
@@ -159,7 +159,8 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
                                                         : (g.ktri == 3 ? (g.tri_first + (n0 / g.tri_cb) * g.tri_stride) * g.tri_cb + n0 % g.tri_cb
                                                                        : 0))) / BK * BK
                           : 0;
-    const int Kt = EXT ? g.K - kskip : g.K;  // this tile's contraction depth
+    // ktri == 4: B (N x K, NT) is lower triangular, B[n][k] = 0 for k > n: the k loop ENDS after the tile's last column
+    const int Kt = EXT ? (g.ktri == 4 ? min(g.K, n0 + BN) : g.K) - kskip : g.K;  // this tile's contraction depth
     const double* Abase = AKC ? (g.A + (int64_t)m0 * g.lda) : (g.A + m0);
     const double* Bbase = BKC ? (g.B + (int64_t)n0 * g.ldb) : (g.B + n0);
     if (EXT) {
@@ -293,7 +294,7 @@ static int launch_impl(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
 // the extended kernel (batch / triangular k range) exists only for the default tile shapes
 template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
 static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
-    if (g.batch > 1 || g.ktri != 0 || g.stair != nullptr) {
+    if (g.batch > 1 || g.ktri != 0) {
         if (KSTEP == 1 && STAGES == 3) return launch_impl<BM, BN, WM, WN, AKC, BKC, 3, MINB, 1, true>(c, g, stream);
         return fail(c, -2, "gemm: batch / triangular k range need the default pipeline (gemm_stages = 3, variant 0 or 1)");
     }

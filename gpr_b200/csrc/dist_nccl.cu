@@ -6,7 +6,8 @@
 // as the torch.distributed form and as the one the CPU gloo tests exercise). What it reproduces of the reference:
 // the result of InvertKernelMatrix + C * Y (lib/GaussianProcess.cpp:531-560, :642-672).
 //
-// Layout. Block (i, j), i >= j, of nb x nb lives on rank (i mod Pr) * Pc + (j mod Pc). A rank keeps ONE local matrix: its
+// Layout. Block (i, j), i >= j, of nb x nb lives on rank rowof(i) * Pc + colof(j) (cyclic maps, the row map mirrored
+// by default: see cyc() below). A rank keeps ONE local matrix: its
 // owned block rows stacked (H rows) by its owned block columns side by side (Wtot columns); block column j uses the rows
 // from its first owned block row i >= j on (the part above is never touched: twice the memory of a packed lower
 // triangle, which buys a trailing update that is ONE tensor-core launch per step - gprb200_gemm_stair_dev - instead of
@@ -38,6 +39,7 @@ struct Problem {
     int64_t N = 0, nb = 0, nblk = 0, H = 0;
     int dim = 0;
     double* dX = nullptr;                    // training inputs (N x dim)
+    double* dXr = nullptr;                   // the owned block rows of dX, stacked (H x dim)
     std::vector<int64_t> hgt, roff;          // block heights; offset of block row i in a stacked panel (-1: not mine)
     std::vector<int64_t> myrows, mine;       // owned block rows / block columns
     double* A = nullptr;                     // the local matrix, H x Wtot (ld LDA)
@@ -74,6 +76,7 @@ struct gprb200_dist {
     Problem P;
     double ms[3] = {0, 0, 0};
     double n_coll = 0, n_bytes = 0, n_flop = 0, launches0 = 0, n_launch = 0;
+    int mirror_rows = 1, mirror_cols = 0;    // options: boustrophedon block-cyclic maps (all ranks must agree)
     int profile = 0;                         // option "profile": timed per-step events on the main stream
     double n_flop_main = 0;                  // flop of the main-stream trailing updates (last learn)
     double stall_ms = 0, busy_ms = 0;        // main stream: waiting for a panel / inside trailing updates (last learn)
@@ -142,6 +145,17 @@ int release_problem(gprb200_dist* d) {
     return 0;
 }
 
+// Grid row of block row i / grid column of block column j. Plain cyclic, or (option "mirror_rows" / "mirror_cols")
+// boustrophedon: 0 1 .. P-1 P-1 .. 1 0, which evens out the lower triangle's bias towards high grid rows and low grid
+// columns (with plain cyclic maps the busiest rank of a 4 x 2 grid at 128 block columns does 7 % more than the mean).
+inline int cyc(int64_t i, int P, int mirror) {
+    if (!mirror || P == 1) return (int)(i % P);
+    const int t = (int)(i % (2 * P));
+    return t < P ? t : 2 * P - 1 - t;
+}
+inline int rowof(const gprb200_dist* d, int64_t i) { return cyc(i, d->Pr, d->mirror_rows); }
+inline int colof(const gprb200_dist* d, int64_t j) { return cyc(j, d->Pc, d->mirror_cols); }
+
 // offset (in rows of a stacked panel) of the first owned block row i >= j, and that i (-1: none)
 inline void first_at_or_after(const gprb200_dist* d, int64_t j, int64_t* offp, int64_t* ip) {
     const Problem& P = d->P;
@@ -173,8 +187,10 @@ int setup_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb) {
     P.N = N; P.nb = nb; P.dim = dim; P.nblk = (N + nb - 1) / nb;
     P.hgt.resize(P.nblk); P.roff.assign(P.nblk, -1);
     for (int64_t i = 0; i < P.nblk; ++i) P.hgt[i] = std::min(nb, N - i * nb);
-    for (int64_t i = d->pr; i < P.nblk; i += d->Pr) { P.roff[i] = P.H; P.H += P.hgt[i]; P.myrows.push_back(i); }
-    for (int64_t j = d->pc; j < P.nblk; j += d->Pc) P.mine.push_back(j);
+    for (int64_t i = 0; i < P.nblk; ++i)
+        if (rowof(d, i) == d->pr) { P.roff[i] = P.H; P.H += P.hgt[i]; P.myrows.push_back(i); }
+    for (int64_t j = 0; j < P.nblk; ++j)
+        if (colof(d, j) == d->pc) P.mine.push_back(j);
     P.cols.assign(P.nblk, nullptr); P.invl.assign(P.nblk, nullptr);
     P.ld.assign(P.nblk, 0); P.off.assign(P.nblk, 0); P.first.assign(P.nblk, -1);
     P.coff.assign(P.nblk, -1);
@@ -204,13 +220,14 @@ int setup_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb) {
             P.colbuf[s].assign(d->Pr, nullptr);
             for (int r2 = 0; r2 < d->Pr; ++r2) {
                 int64_t cnt = 0;
-                for (int64_t j : P.mine) if (j % d->Pr == r2) cnt += P.hgt[j];
+                for (int64_t j : P.mine) if (rowof(d, j) == r2) cnt += P.hgt[j];
                 RK(dmalloc(d, (void**)&P.colbuf[s][r2], (size_t)std::max<int64_t>(cnt, 1) * nb * 8));
             }
         }
     }
     RK(dmalloc(d, (void**)&P.eye, (size_t)nb * nb * 8));
     RK(dmalloc(d, (void**)&P.dX, (size_t)N * dim * 8));
+    RK(dmalloc(d, (void**)&P.dXr, (size_t)std::max<int64_t>(P.H, 1) * dim * 8));
     RK(dmalloc(d, (void**)&P.dinfo, 256));
     RK(dmalloc(d, (void**)&P.dflag, 256));
     RK(dmalloc(d, (void**)&P.dsum, 256));
@@ -236,10 +253,11 @@ int build_gram(gprb200_dist* d) {
             GK(d->hm, gprb200_gram_block_dev(d->hm, j * P.nb, P.H - P.off[j], j * P.nb, P.hgt[j], P.cols[j], P.ld[j]));
             continue;
         }
-        for (int64_t i : P.myrows)
-            if (i >= j)
-                GK(d->hm, gprb200_gram_block_dev(d->hm, i * P.nb, P.hgt[i], j * P.nb, P.hgt[j],
-                                                 P.cols[j] + (P.roff[i] - P.off[j]) * P.ld[j], P.ld[j]));
+        // the owned rows below are not contiguous in the sample list: one launch against the gathered rows, then the
+        // diagonal block again through gram_block (which adds sigma^2 on the global diagonal)
+        GK(d->hm, gprb200_gram_pair_dev(d->hm, P.dXr + P.off[j] * P.dim, P.H - P.off[j], P.dX + j * P.nb * P.dim, P.hgt[j],
+                                        P.cols[j], P.ld[j]));
+        if (P.first[j] == j) GK(d->hm, gprb200_gram_block_dev(d->hm, j * P.nb, P.hgt[j], j * P.nb, P.hgt[j], P.cols[j], P.ld[j]));
     }
     P.factored = false;
     return 0;
@@ -250,9 +268,9 @@ int build_gram(gprb200_dist* d) {
 // below; X is left in the row buffer k % 2 AND in cols[k] (the factor, needed by the solve).
 int panel_factor(gprb200_dist* d, int64_t k) {
     Problem& P = d->P;
-    if (k % d->Pc != d->pc) return 0;
+    if (colof(d, k) != d->pc) return 0;
     const int64_t w = P.hgt[k], nb = P.nb;
-    const bool diag = (k % d->Pr == d->pr);
+    const bool diag = (rowof(d, k) == d->pr);
     if (diag) GK(d->hp, gprb200_potrf_panel_async_dev(d->hp, P.cols[k], P.ld[k], w, w, P.invl[k], k * nb, P.dinfo));
     if (k == P.nblk - 1) return 0;          // nothing below the last diagonal block (and w == nb everywhere else)
     double* W = P.W[k % 2];
@@ -260,15 +278,15 @@ int panel_factor(gprb200_dist* d, int64_t k) {
         CK(cudaMemcpyAsync(W, P.eye, (size_t)nb * nb * 8, cudaMemcpyDeviceToDevice, d->sp));
         GK(d->hp, gprb200_trsm_dev(d->hp, P.cols[k], P.ld[k], P.invl[k], w, W, nb, nb, 0));
     }
-    if (d->Pr > 1) RK(bcast(d, W, nb * nb, (int)(k % d->Pr), d->col_comm, d->sp));
+    if (d->Pr > 1) RK(bcast(d, W, nb * nb, rowof(d, k), d->col_comm, d->sp));
     int64_t o1, first;
     first_at_or_after(d, k + 1, &o1, &first);
     if (first < 0) return 0;
     double* below = P.cols[k] + (o1 - P.off[k]) * P.ld[k];
     double* X = P.row[k % 2];
     const int64_t rows = P.H - o1;
-    GK(d->hp, gprb200_gemm_dev(d->hp, 0, rows, w, w, 1.0, below, P.ld[k], W, nb, 0.0, X, nb, 0));
-    d->n_flop += 2.0 * rows * w * w;
+    GK(d->hp, gprb200_gemm_dev(d->hp, 3, rows, w, w, 1.0, below, P.ld[k], W, nb, 0.0, X, nb, 0));    // W is lower triangular
+    d->n_flop += 1.0 * rows * w * (w + 64);
     CK(cudaMemcpy2DAsync(below, (size_t)P.ld[k] * 8, X, (size_t)nb * 8, (size_t)w * 8, (size_t)rows, cudaMemcpyDeviceToDevice, d->sp));
     return 0;
 }
@@ -282,7 +300,7 @@ int distribute(gprb200_dist* d, int64_t k) {
     int64_t o1, first;
     first_at_or_after(d, k + 1, &o1, &first);
     double* X = P.row[k % 2];
-    if (d->Pc > 1 && first >= 0) RK(bcast(d, X, (P.H - o1) * nb, (int)(k % d->Pc), d->row_comm, d->sp));
+    if (d->Pc > 1 && first >= 0) RK(bcast(d, X, (P.H - o1) * nb, colof(d, k), d->row_comm, d->sp));
     double* B = P.Bop[k % 2];
     auto jbeg = std::upper_bound(P.mine.begin(), P.mine.end(), k);
     if (jbeg == P.mine.end()) return 0;
@@ -298,10 +316,10 @@ int distribute(gprb200_dist* d, int64_t k) {
     }
     std::vector<int64_t> total(d->Pr, 0);
     int groups = 0;
-    for (auto it = jbeg; it != P.mine.end(); ++it) total[*it % d->Pr] += P.hgt[*it];
+    for (auto it = jbeg; it != P.mine.end(); ++it) total[rowof(d, *it)] += P.hgt[*it];
     for (int r2 = 0; r2 < d->Pr; ++r2) groups += total[r2] > 0;
     if (groups == 1) {  // (Pc a multiple of Pr: all owned block columns meet the same grid row) straight into B
-        const int r2 = (int)(*jbeg % d->Pr);
+        const int r2 = rowof(d, *jbeg);
         if (r2 == d->pr)
             for (auto it = jbeg; it != P.mine.end(); ++it)
                 RK(copy_block(B + (P.coff[*it] - c0) * nb, X + (P.roff[*it] - o1) * nb, P.hgt[*it]));
@@ -309,7 +327,7 @@ int distribute(gprb200_dist* d, int64_t k) {
     }
     std::vector<int64_t> pos(d->Pr, 0);
     for (auto it = jbeg; it != P.mine.end(); ++it) {
-        const int r2 = (int)(*it % d->Pr);
+        const int r2 = rowof(d, *it);
         if (r2 == d->pr) RK(copy_block(P.colbuf[k % 2][r2] + pos[r2] * nb, X + (P.roff[*it] - o1) * nb, P.hgt[*it]));
         pos[r2] += P.hgt[*it];
     }
@@ -319,7 +337,7 @@ int distribute(gprb200_dist* d, int64_t k) {
     NK(ncclGroupEnd());
     std::fill(pos.begin(), pos.end(), 0);
     for (auto it = jbeg; it != P.mine.end(); ++it) {
-        const int r2 = (int)(*it % d->Pr);
+        const int r2 = rowof(d, *it);
         RK(copy_block(B + (P.coff[*it] - c0) * nb, P.colbuf[k % 2][r2] + pos[r2] * nb, P.hgt[*it]));
         pos[r2] += P.hgt[*it];
     }
@@ -353,7 +371,7 @@ int factor(gprb200_dist* d, int* info_out) {
     CK(cudaStreamWaitEvent(d->sp, d->ev_gram, 0));
     RK(panel_factor(d, 0));
     for (int64_t k = 0; k < nblk; ++k) {
-        const bool nxt_mine = k + 1 < nblk && (k + 1) % d->Pc == d->pc;
+        const bool nxt_mine = k + 1 < nblk && colof(d, k + 1) == d->pc;
         if (k >= 2) CK(cudaStreamWaitEvent(d->sp, P.ev_main[k - 2], 0));     // buffers k % 2 were last read at step k - 2
         RK(distribute(d, k));
         CK(cudaEventRecord(P.ev_panel[k], d->sp));
@@ -453,7 +471,7 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
     int64_t ndiag = 0;
     std::vector<int64_t> zoff(nblk, -1);
     for (int64_t k = 0; k < nblk; ++k)
-        if (k % d->Pr == d->pr && k % d->Pc == d->pc) { zoff[k] = ndiag; ndiag += P.hgt[k]; }
+        if (rowof(d, k) == d->pr && colof(d, k) == d->pc) { zoff[k] = ndiag; ndiag += P.hgt[k]; }
     double* stage = nullptr;     // contiguous N x M image of the host array (a pitched copy of 8-byte rows crawls)
     if ((rc = talloc(&y, (size_t)N * ld)) || (rc = talloc(&out, (size_t)N * ld)) || (rc = talloc(&stage, (size_t)N * M)) ||
         (rc = talloc(&acc, (size_t)std::max<int64_t>(P.H, 1) * ld)) || (rc = talloc(&msg[0], (size_t)nb * ld)) ||
@@ -472,12 +490,12 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
         // ---- forward
         for (int64_t k = 0; k < nblk; ++k) {
             const int64_t w = P.hgt[k];
-            const bool in_row = (k % d->Pr == d->pr), in_col = (k % d->Pc == d->pc), diag = in_row && in_col;
+            const bool in_row = (rowof(d, k) == d->pr), in_col = (colof(d, k) == d->pc), diag = in_row && in_col;
             double* buf = msg[k % 2];
             if (in_row) {
                 double* part = acc + P.roff[k] * ld;
                 if (d->Pc > 1) {
-                    NK(ncclReduce(part, part, (size_t)(w * ld), ncclDouble, ncclSum, (int)(k % d->Pc), d->row_comm, st));
+                    NK(ncclReduce(part, part, (size_t)(w * ld), ncclDouble, ncclSum, colof(d, k), d->row_comm, st));
                     d->n_coll += 1; d->n_bytes += 8.0 * w * ld;
                 }
                 if (diag) {
@@ -488,7 +506,7 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
                 }
             }
             if (!in_col || k == nblk - 1) continue;
-            if (d->Pr > 1) RK(bcast(d, buf, nb * ld, (int)(k % d->Pr), d->col_comm, st));
+            if (d->Pr > 1) RK(bcast(d, buf, nb * ld, rowof(d, k), d->col_comm, st));
             int64_t o1, first;
             first_at_or_after(d, k + 1, &o1, &first);
             if (first >= 0)
@@ -498,7 +516,7 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
         // ---- backward: acc now collects x_i for the owned rows
         for (int64_t k = nblk - 1; k >= 0; --k) {
             const int64_t w = P.hgt[k];
-            const bool in_row = (k % d->Pr == d->pr), in_col = (k % d->Pc == d->pc), diag = in_row && in_col;
+            const bool in_row = (rowof(d, k) == d->pr), in_col = (colof(d, k) == d->pc), diag = in_row && in_col;
             double* buf = msg[k % 2];
             if (in_col) {
                 int64_t o1, first;
@@ -509,7 +527,7 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
                 else
                     CK(cudaMemsetAsync(buf, 0, (size_t)w * ld * 8, st));
                 if (d->Pr > 1) {
-                    NK(ncclReduce(buf, buf, (size_t)(nb * ld), ncclDouble, ncclSum, (int)(k % d->Pr), d->col_comm, st));
+                    NK(ncclReduce(buf, buf, (size_t)(nb * ld), ncclDouble, ncclSum, rowof(d, k), d->col_comm, st));
                     d->n_coll += 1; d->n_bytes += 8.0 * nb * ld;
                 }
                 if (diag) {
@@ -519,7 +537,7 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
                 }
             }
             if (in_row) {
-                if (d->Pc > 1) RK(bcast(d, buf, nb * ld, (int)(k % d->Pc), d->row_comm, st));
+                if (d->Pc > 1) RK(bcast(d, buf, nb * ld, colof(d, k), d->row_comm, st));
                 CK(cudaMemcpyAsync(acc + P.roff[k] * ld, buf, (size_t)w * ld * 8, cudaMemcpyDeviceToDevice, st));
             }
         }
@@ -621,10 +639,10 @@ int gprb200_dist_create(gprb200_dist_handle* out, int device, int rank, int worl
     *out = nullptr;
     if (world < 1 || rank < 0 || rank >= world) return fail(d, -2, "gprb200_dist_create: rank / world out of range");
     if (world > 1 && !id) return fail(d, -2, "gprb200_dist_create: unique id needed when world > 1");
-    if (Pr == 0 && Pc == 0) {
-        Pr = 1;
-        while ((2 * Pr) * (2 * Pr) <= world && world % (2 * Pr) == 0) Pr *= 2;
-        Pc = world / Pr;
+    if (Pr == 0 && Pc == 0) {   // tall: 8 -> 4 x 2, 4 -> 2 x 2, 2 -> 2 x 1 (measured: profiles/r02_c5_grid_comparison.json)
+        Pc = 1;
+        while ((2 * Pc) * (2 * Pc) <= world && world % (2 * Pc) == 0) Pc *= 2;
+        Pr = world / Pc;
     }
     if (Pr < 1 || Pc < 1 || Pr * Pc != world) return fail(d, -2, "gprb200_dist_create: Pr * Pc must equal world");
     gprb200_dist* n = new gprb200_dist();
@@ -654,6 +672,11 @@ int gprb200_dist_set_option(gprb200_dist_handle d, const char* name, int64_t val
         release_problem(d);
         return 0;
     }
+    if (name && (std::strcmp(name, "mirror_rows") == 0 || std::strcmp(name, "mirror_cols") == 0)) {
+        (name[7] == 'r' ? d->mirror_rows : d->mirror_cols) = value != 0;
+        release_problem(d);
+        return 0;
+    }
     GK(d->hm, gprb200_set_option(d->hm, name, value));
     GK(d->hp, gprb200_set_option(d->hp, name, value));
     return 0;
@@ -673,6 +696,10 @@ int gprb200_dist_learn(gprb200_dist_handle d, const double* X, int64_t N, int di
     RK(setup_problem(d, N, dim, nb));
     CK(cudaMemcpyAsync(d->P.dX, X, (size_t)N * dim * 8, cudaMemcpyHostToDevice, d->sm));
     GK(d->hm, gprb200_set_train_dev(d->hm, d->P.dX, N, dim, nullptr, 0, sigma));
+    if (d->Pr > 1)
+        for (int64_t i : d->P.myrows)
+            CK(cudaMemcpyAsync(d->P.dXr + d->P.roff[i] * dim, d->P.dX + i * nb * dim, (size_t)d->P.hgt[i] * dim * 8,
+                               cudaMemcpyDeviceToDevice, d->sm));
     CK(cudaEventRecord(d->t0, d->sm));
     RK(build_gram(d));
     CK(cudaEventRecord(d->t1, d->sm));
@@ -725,6 +752,8 @@ double gprb200_dist_counter(gprb200_dist_handle d, int which) {
         case 4: return d->stall_ms;
         case 5: return d->busy_ms;
         case 6: return d->n_flop_main;
+        case 7: return d->Pr;
+        case 8: return d->Pc;
     }
     return -1.0;
 }

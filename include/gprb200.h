@@ -160,7 +160,9 @@ int gprb200_lu_inverse(gprb200_handle h, const double* A, int64_t n, double* Ain
 
 /* ---- device-pointer building blocks (multi-GPU drivers, probes) -------------------------------------- */
 /* C = alpha op(A) op(B) + beta C on the FP64 tensor path, row-major, device pointers, 16-byte aligned, even lds.
- * form 0 (NT): A is M x K, B is N x K, C = A B^T; 1 (NN): B is K x N; 2 (TN): A is K x M, B is K x N, C = A^T B.
+ * form 0 (NT): A is M x K, B is N x K, C = A B^T; 1 (NN): B is K x N; 2 (TN): A is K x M, B is K x N, C = A^T B;
+ * 3: as 0 with B LOWER TRIANGULAR (B[n][k] = 0 for k > n; entries above the diagonal are not read beyond the tile's
+ * last column): the product with an inverted Cholesky block, X = A inv(L)^T, at half the flop.
  * lower != 0 (square C): only tiles meeting the lower triangle are computed (SYRK-style trailing update).
  * Replaces the Eigen / BLAS products of lib/GaussianProcess.cpp:60, :661. */
 int gprb200_gemm_dev(gprb200_handle h, int form, int64_t M, int64_t N, int64_t K, double alpha, const double* dA,
@@ -180,6 +182,11 @@ int gprb200_gemm_stair_dev(gprb200_handle h, int64_t M, int64_t N, int64_t K, do
  * a multi-GPU factorisation build exactly the block columns it owns, with no exchange. */
 int gprb200_gram_block_dev(gprb200_handle h, int64_t row0, int64_t nrows, int64_t col0, int64_t ncols, double* dOut,
                            int64_t ldo);
+/* k(a_i, b_j) for two explicit DEVICE sample sets (na x d and nb x d, d the dimension of the installed samples), no noise
+ * term: ComputeKernelMatrix (lib/GaussianProcess.cpp:363-402) for rows that are not contiguous in the sample list - a
+ * rank of a 2-D block-cyclic grid gathers its block rows once and builds each owned block column in one launch. */
+int gprb200_gram_pair_dev(gprb200_handle h, const double* dXa, int64_t na, const double* dXb, int64_t nb, double* dOut,
+                          int64_t ldo);
 /* One block column of the Cholesky factor: dP is rows x w (ld), its top w x w block is factored in place and the
  * rows below are solved against it (the dpotrf + dtrsm a blocked LAPACK dpotrf does per panel;
  * include/LAPACKUtils.h:59-73). dInvL: ceil(w/128) blocks of 128 x 128 (inverted diagonal blocks, for trsm_dev). */

@@ -31,7 +31,10 @@ typedef struct gprb200_dist* gprb200_dist_handle;
 /* Rank 0 only: fills id[GPRB200_DIST_ID_BYTES] (ncclGetUniqueId). */
 int gprb200_dist_get_unique_id(void* id);
 /* Every rank: device = CUDA ordinal of this rank's GPU; Pr * Pc == world; rank r sits at grid row r / Pc, grid column
- * r % Pc. Pr = Pc = 0 picks the default grid (largest power of two Pr with Pr^2 <= world dividing world: 8 -> 2 x 4). */
+ * r % Pc. Pr = Pc = 0 picks the default grid (tall: Pc the largest power of two with Pc^2 <= world dividing world;
+ * 8 -> 4 x 2, 4 -> 2 x 2, 2 -> 2 x 1). Block row i lives on grid row 0 1 .. Pr-1 Pr-1 .. 1 0 0 1 .. (mirrored cyclic,
+ * which evens out the lower triangle's bias; option "mirror_rows" 0 gives the plain i mod Pr), block column j on grid
+ * column j mod Pc (option "mirror_cols"). */
 int gprb200_dist_create(gprb200_dist_handle* out, int device, int rank, int world, const void* id, int Pr, int Pc);
 int gprb200_dist_destroy(gprb200_dist_handle d);
 const char* gprb200_dist_last_error(gprb200_dist_handle d); /* d may be NULL: last create() error of this thread */
@@ -39,7 +42,8 @@ const char* gprb200_dist_last_error(gprb200_dist_handle d); /* d may be NULL: la
 /* The kernel in the op-code form of gprb200_set_kernel (gprb200.h; KernelFactory::GetKernel, include/KernelFactory.h). */
 int gprb200_dist_set_kernel(gprb200_dist_handle d, const int32_t* ops, int nops, const double* params, int nparams);
 /* Options of the LOCAL single-GPU library handles (gprb200_set_option names, e.g. "gemm_small"), both streams; and
- * "profile" (0 / 1): timed events around every trailing update, for counters 4 and 5 below. */
+ * "profile" (0 / 1): timed events around every trailing update, for counters 4 and 5 below; "mirror_rows" /
+ * "mirror_cols" (0 / 1, the same on every rank): the block-to-grid maps described at gprb200_dist_create. */
 int gprb200_dist_set_option(gprb200_dist_handle d, const char* name, int64_t value);
 
 /* Learn: X is N x dim, Y is N x M (row-major HOST arrays, the same on every rank; M small - many outputs shard by
@@ -58,7 +62,7 @@ int gprb200_dist_solve(gprb200_dist_handle d, const double* Y, int64_t M, double
 double gprb200_dist_phase_ms(gprb200_dist_handle d, int which);
 /* Counters of the last learn on this rank: 0 NCCL calls issued, 1 bytes broadcast / reduced, 2 GEMM flop issued,
  * 3 kernels launched through libgprb200.so; with option "profile": 4 ms the main stream waited for a panel, 5 ms it spent
- * inside trailing updates, 6 the flop of those updates (factorisation only). */
+ * inside trailing updates, 6 the flop of those updates (factorisation only); 7 / 8: Pr / Pc of the grid in use. */
 double gprb200_dist_counter(gprb200_dist_handle d, int which);
 
 #ifdef __cplusplus

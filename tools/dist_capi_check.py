@@ -49,7 +49,7 @@ def main():
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         c = d.counters()
         stall = tm[4].item()
-        out = {"N": N, "nb": nb, "world": world, "grid": sys.argv[3] if grid else "default", "impl": "libgprb200_dist.so (NCCL from C++)",
+        out = {"N": N, "nb": nb, "world": world, "grid": "%dx%d" % (c["Pr"], c["Pc"]), "impl": "libgprb200_dist.so (NCCL from C++)",
                "gram_s": tm[0].item() * 1e-3, "factor_s": tm[1].item() * 1e-3, "solve_s": tm[2].item() * 1e-3,
                "learn_wall_s_host_to_host": tm[3].item() * 1e-3, "factor_TFs_total": N ** 3 / 3.0 / (tm[1].item() * 1e-3) * 1e-12,
                "stall_ms_max_over_ranks": stall, "busy_ms": c["busy_ms"], "gemm_TFs_inside_updates_this_rank": (c["update_flops"] / c["busy_ms"] * 1e-9 if c["busy_ms"] > 0 else None),
