@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgprb200.so")
+LIB_PATH = os.environ.get("GPRB200_LIB") or os.path.join(_HERE, "libgprb200.so")   # override: A/B builds (tools/)
 
 # every symbol include/gprb200.h declares (tests/test_abi.py checks header <-> library <-> this table)
 _PROTOS = {
@@ -116,6 +116,8 @@ def load_library():
             "gpr_b200 has no CPU fallback")
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in _PROTOS.items():
+        if os.environ.get("GPRB200_LIB") and not hasattr(lib, name):
+            continue  # an older A/B build (tools/lib_ab.py) may lack the newest entry points
         fn = getattr(lib, name)  # AttributeError here means header and library diverged
         fn.restype = res
         fn.argtypes = args

@@ -869,7 +869,7 @@ int gprb200_gemm_stair_dev(gprb200_handle h, int64_t M, int64_t N, int64_t K, do
     GemmArgs g{};
     g.A = dA; g.lda = lda; g.B = dB; g.ldb = ldb; g.C = dC; g.ldc = ldc;
     g.M = (int)M; g.N = (int)N; g.K = (int)K; g.alpha = alpha; g.beta = beta;
-    g.stair = dStair; g.stair_row0 = (int)row0;
+    g.set_stair(dStair, (int)row0);
     return gemm(c, GEMM_NT, g);
 }
 

@@ -39,14 +39,19 @@ struct GemmArgs {
     //      is global column (tri_first + (n / tri_cb) * tri_stride) * tri_cb + n % tri_cb, and B[k][n] = 0 for k < that
     //   4: NT form, B (N x K) is lower triangular, B[n][k] = 0 for k > n  ->  k ENDS after the tile's last column (the
     //      product with an inverted Cholesky block: X = A inv(L)^T)
+    //   5: "staircase" C, the trailing update of a block-cyclic Cholesky in ONE launch (no k skip). stair() is a device
+    //      table: entry u is the first row (in the caller's row numbering) that columns [64 u, 64 u + 64) of C need; row r
+    //      of C carries the number stair_row0() + r. A tile whose rows all lie before the stair of all of its columns exits
+    //      at once. The table pointer and the row number travel in sC and tri_first, which mode 5 does not use otherwise:
+    //      the struct stays at 128 bytes - growing the kernel's parameter block by 16 bytes cost the single-GPU
+    //      Cholesky 4 % (364 -> 380 ms at N = 32768, same SASS instruction mix; profiles/r02_gemmargs_ab.md).
     int ktri;
     int tri_cb, tri_first, tri_stride;
-    // stair (device, may be null): "staircase" C, the trailing update of a block-cyclic Cholesky in ONE launch. Entry u is
-    // the first row (in the caller's row numbering) that columns [64 u, 64 u + 64) of C need; row r of C carries the
-    // number stair_row0 + r. A tile whose rows all lie before the stair of all of its columns exits at once.
-    const int* stair;
-    int stair_row0;
+    __host__ __device__ const int* stair() const { return ktri == 5 ? reinterpret_cast<const int*>(sC) : nullptr; }
+    __host__ __device__ int stair_row0() const { return tri_first; }
+    void set_stair(const int* table, int row0) { ktri = 5; sC = reinterpret_cast<int64_t>(table); tri_first = row0; }
 };
+static_assert(sizeof(GemmArgs) == 128, "GemmArgs is a kernel parameter: keep its size");
 
 enum GemmForm { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };
 

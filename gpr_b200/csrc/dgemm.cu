@@ -128,7 +128,9 @@ struct FastLoader {
 // EXT = false is the Cholesky / solve hot path: no batch index, no triangular k range (the 64x16 variant sits exactly at
 // its 128-register cap; carrying the extra strides and offsets cost 3 % of the factorisation when it was unconditional).
 template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1, bool EXT = false>
-__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel(GemmArgs g, int tiles_m, int tiles_n) {
+__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel(GemmArgs g) {
+    // (the tile counts are recomputed here rather than passed: the parameter block stays at sizeof(GemmArgs) = 128 bytes)
+    const int tiles_m = (g.M + BM - 1) / BM, tiles_n = (g.N + BN - 1) / BN;
     constexpr int THREADS = (BM / WM) * (BN / WN) * 32;
     constexpr int WARPS_N = BN / WN;
     constexpr int FM = WM / 8, FN = WN / 8;
@@ -142,10 +144,11 @@ __global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32, MINB) dgemm_kernel
     if (!map_tile<BM, BN>(blockIdx.x, g.lower, tiles_m, tiles_n, ti, tj)) return;
     const int m0 = ti * BM, n0 = tj * BN;
     if (m0 >= g.M || n0 >= g.N) return;
-    if (g.stair != nullptr) {   // staircase C: nothing of this tile is below the stair of its columns
-        int first = g.stair[n0 >> 6];
-        if (BN > 64 && n0 + 64 < g.N) first = min(first, g.stair[(n0 >> 6) + 1]);
-        if (g.stair_row0 + m0 + BM <= first) return;
+    if (g.ktri == 5) {   // staircase C: nothing of this tile is below the stair of its columns
+        const int* stair = g.stair();
+        int first = stair[n0 >> 6];
+        if (BN > 64 && n0 + 64 < g.N) first = min(first, stair[(n0 >> 6) + 1]);
+        if (g.stair_row0() + m0 + BM <= first) return;
     }
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -285,7 +288,7 @@ static int launch_impl(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
         grid = tm * tn;
     }
     if (grid <= 0) return 0;
-    kern<<<dim3((unsigned)grid, (unsigned)(g.batch > 1 ? g.batch : 1)), THREADS, SMEM, stream>>>(g, (int)tm, (int)tn);
+    kern<<<dim3((unsigned)grid, (unsigned)(g.batch > 1 ? g.batch : 1)), THREADS, SMEM, stream>>>(g);
     ++c->launches;
     GP_CUDA(c, cudaGetLastError());
     return 0;
@@ -294,7 +297,7 @@ static int launch_impl(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
 // the extended kernel (batch / triangular k range) exists only for the default tile shapes
 template <int BM, int BN, int WM, int WN, bool AKC, bool BKC, int STAGES, int MINB, int KSTEP = 1>
 static int launch(Ctx* c, const GemmArgs& g, cudaStream_t stream) {
-    if (g.batch > 1 || g.ktri != 0) {
+    if (g.batch > 1 || (g.ktri != 0 && g.ktri != 5)) {
         if (KSTEP == 1 && STAGES == 3) return launch_impl<BM, BN, WM, WN, AKC, BKC, 3, MINB, 1, true>(c, g, stream);
         return fail(c, -2, "gemm: batch / triangular k range need the default pipeline (gemm_stages = 3, variant 0 or 1)");
     }
@@ -328,7 +331,7 @@ int gemm(Ctx* c, GemmForm form, const GemmArgs& g, cudaStream_t stream) {
     // short-K products with one column tile (the K = 128 panel solves and next-block-column updates of potrf.cu):
     // a 128 x 128 x 128 product is 17 us of DMMA on ONE SM, and a tall panel has only m / 128 such CTAs; 32-row tiles
     // give four times the CTAs at a quarter of the latency each
-    if (wide && form == GEMM_NT && g.K <= 256 && c->opt_gemm_small && g.batch <= 1 && g.ktri == 0 && !g.stair)
+    if (wide && form == GEMM_NT && g.K <= 256 && c->opt_gemm_small && g.batch <= 1 && g.ktri == 0)
         return launch<32, 128, 16, 32, true, true, 3, 2>(c, g, stream);
     switch (form) {
         case GEMM_NT:

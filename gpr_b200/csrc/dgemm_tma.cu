@@ -240,7 +240,7 @@ static int make_map(Ctx* c, CUtensorMap* m, const double* base, int64_t rows, in
 }
 
 bool gemm_tma_eligible(const Ctx* c, GemmForm form, const GemmArgs& g) {
-    if (!c->opt_gemm_tma || form != GEMM_NT || g.batch > 1 || g.ktri != 0 || g.stair) return false;
+    if (!c->opt_gemm_tma || form != GEMM_NT || g.batch > 1 || g.ktri != 0) return false;
     if (g.C == g.A || g.C == g.B) return false;                       // in-place panel solves keep the CTA-owned kernel
     if (g.K < c->opt_gemm_tma_min_k) return false;                    // short K: the pipeline fill dominates
     const int64_t tm = (g.M + TBM - 1) / TBM, tn = (g.N + TBN - 1) / TBN;

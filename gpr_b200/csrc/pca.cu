@@ -231,20 +231,38 @@ __global__ void __launch_bounds__(PT) pca_project_kernel(const double* __restric
     for (int64_t i0 = r0 + grp * PU; i0 < r1; i0 += (PT / 16) * PU) {
         double2 b[PU];
         double xc[PU][NC];
+        if (i0 + PU <= r1 && live1 && T == NC) {
+            // whole group of rows, both modes, all columns: every load is issued before the first use (with the per-row
+            // bounds checks below, the subtraction after each row's loads kept ONE row in flight per thread: 40 % of HBM)
+            double mu[PU];
 #pragma unroll
-        for (int u = 0; u < PU; ++u) {
-            const int64_t i = i0 + u;
-            b[u] = make_double2(0.0, 0.0);
-            if (i < r1) {
-                const double* src = B + i * ldb + k;  // ldb even, k even: 16-byte aligned
-                if (live1) b[u] = __ldcs(reinterpret_cast<const double2*>(src));
-                else if (live0) b[u].x = __ldcs(src);
-                const double mu = mean[i];
+            for (int u = 0; u < PU; ++u) b[u] = __ldcs(reinterpret_cast<const double2*>(B + (i0 + u) * ldb + k));
 #pragma unroll
-                for (int t = 0; t < NC; ++t) xc[u][t] = (t < T) ? X[i * ldx + t] - mu : 0.0;
-            } else {
+            for (int u = 0; u < PU; ++u) mu[u] = mean[i0 + u];
 #pragma unroll
-                for (int t = 0; t < NC; ++t) xc[u][t] = 0.0;
+            for (int u = 0; u < PU; ++u)
+#pragma unroll
+                for (int t = 0; t < NC; ++t) xc[u][t] = X[(i0 + u) * ldx + t];
+#pragma unroll
+            for (int u = 0; u < PU; ++u)
+#pragma unroll
+                for (int t = 0; t < NC; ++t) xc[u][t] -= mu[u];
+        } else {
+#pragma unroll
+            for (int u = 0; u < PU; ++u) {
+                const int64_t i = i0 + u;
+                b[u] = make_double2(0.0, 0.0);
+                if (i < r1) {
+                    const double* src = B + i * ldb + k;  // ldb even, k even: 16-byte aligned
+                    if (live1) b[u] = __ldcs(reinterpret_cast<const double2*>(src));
+                    else if (live0) b[u].x = __ldcs(src);
+                    const double mu = mean[i];
+#pragma unroll
+                    for (int t = 0; t < NC; ++t) xc[u][t] = (t < T) ? X[i * ldx + t] - mu : 0.0;
+                } else {
+#pragma unroll
+                    for (int t = 0; t < NC; ++t) xc[u][t] = 0.0;
+                }
             }
         }
 #pragma unroll
