@@ -33,6 +33,7 @@ template <class TScalarType>
 class Likelihood;
 
 namespace detail {
+struct DistModel;    // opaque: libgprb200_dist.so handle of this rank (src/GaussianProcess.cpp)
 struct DeviceModel;  // opaque: gprb200 handle + what has been sent to it (src/GaussianProcess.cpp)
 }
 
@@ -100,6 +101,15 @@ public:
     DeterminantMode GetDeterminantMode() const { return m_DeterminantMode; }
     // CUDA device this model lives on (default: $GPRB200_DEVICE or 0); call before the first use
     void SetDevice(int device);
+    // ONE model over several GPUs (not in the reference, which is a single process; include/gprb200_dist.h). Call on
+    // every rank - one process or thread per GPU, each with its own GaussianProcess holding the same samples - before
+    // Initialize(): ComputeRegressionVectors then factors K + sigma^2 I on the Pr x Pc grid of GPUs (block-cyclic
+    // Cholesky, NCCL) and every rank keeps the regression vectors, so Predict runs locally on each. nccl_id: the
+    // GetDistributedId() bytes of rank 0, carried to the other ranks by the application (MPI_Bcast, a file, ...);
+    // world == 1 needs none. Pr = Pc = 0: the library's default grid. libgprb200_dist.so is opened on first use, so
+    // programs that never call this do not need NCCL.
+    void SetDistributed(int rank, int world, const void* nccl_id, int Pr = 0, int Pc = 0);
+    static std::vector<unsigned char> GetDistributedId();
     // milliseconds of the last Gram / Cholesky / solve / inverse / predict phases (CUDA events)
     std::vector<double> GetPhaseMilliseconds() const;
     // The gprb200_handle (include/gprb200.h) this model lives on, initialised and in sync with the host state.
@@ -179,6 +189,8 @@ private:
     detail::DeviceModel& Device() const;
     void SyncModelToDevice() const;  // kernel program, samples/labels, sigma
     mutable std::unique_ptr<detail::DeviceModel> m_Device;
+    std::shared_ptr<detail::DistModel> m_Dist;   // set by SetDistributed
+    void ComputeRegressionVectorsDistributed();
     mutable bool m_TrainDirty;
     mutable bool m_AlphaMirrored;
     mutable bool m_CoreMirrored;

@@ -9,12 +9,14 @@
 #include <limits>
 #include <sstream>
 #include <type_traits>
+#include <dlfcn.h>
 #include <sys/stat.h>
 
 #include "GaussianProcess.h"
 #include "KernelFactory.h"
 #include "MatrixIO.h"
 #include "gprb200.h"
+#include "gprb200_dist.h"
 
 namespace gpr {
 
@@ -35,6 +37,50 @@ struct DeviceModel {
     }
     void Check(int rc) const {
         if (rc != 0) throw std::string(gprb200_last_error(h));
+    }
+};
+
+// libgprb200_dist.so, opened on first use (it needs NCCL; libgplib.so must not), and this rank's handle in it
+struct DistLib {
+    void* so = nullptr;
+    decltype(&gprb200_dist_get_unique_id) get_unique_id = nullptr;
+    decltype(&gprb200_dist_create) create = nullptr;
+    decltype(&gprb200_dist_destroy) destroy = nullptr;
+    decltype(&gprb200_dist_last_error) last_error = nullptr;
+    decltype(&gprb200_dist_set_kernel) set_kernel = nullptr;
+    decltype(&gprb200_dist_learn) learn = nullptr;
+
+    static DistLib& Get() {
+        static DistLib lib;
+        if (!lib.so) {
+            lib.so = ::dlopen("libgprb200_dist.so", RTLD_NOW | RTLD_GLOBAL);   // found through libgplib.so's RUNPATH
+            if (!lib.so) throw std::string("GaussianProcess::SetDistributed: cannot open libgprb200_dist.so: ") + ::dlerror();
+            auto sym = [&](const char* name) {
+                void* p = ::dlsym(lib.so, name);
+                if (!p) throw std::string("GaussianProcess::SetDistributed: libgprb200_dist.so lacks ") + name;
+                return p;
+            };
+            lib.get_unique_id = reinterpret_cast<decltype(lib.get_unique_id)>(sym("gprb200_dist_get_unique_id"));
+            lib.create = reinterpret_cast<decltype(lib.create)>(sym("gprb200_dist_create"));
+            lib.destroy = reinterpret_cast<decltype(lib.destroy)>(sym("gprb200_dist_destroy"));
+            lib.last_error = reinterpret_cast<decltype(lib.last_error)>(sym("gprb200_dist_last_error"));
+            lib.set_kernel = reinterpret_cast<decltype(lib.set_kernel)>(sym("gprb200_dist_set_kernel"));
+            lib.learn = reinterpret_cast<decltype(lib.learn)>(sym("gprb200_dist_learn"));
+        }
+        return lib;
+    }
+};
+
+struct DistModel {
+    gprb200_dist_handle d = nullptr;
+    double logdet = 0.0;
+    DistModel(int device, int rank, int world, const void* id, int Pr, int Pc) {
+        DistLib& lib = DistLib::Get();
+        if (lib.create(&d, device, rank, world, id, Pr, Pc) != 0)
+            throw std::string("GaussianProcess::SetDistributed: ") + lib.last_error(nullptr);
+    }
+    ~DistModel() {
+        if (d) DistLib::Get().destroy(d);
     }
 };
 
@@ -191,9 +237,67 @@ void GaussianProcess<TScalarType>::Initialize() {
     m_Initialized = true;
 }
 
+template <class TScalarType>
+std::vector<unsigned char> GaussianProcess<TScalarType>::GetDistributedId() {
+    std::vector<unsigned char> id(GPRB200_DIST_ID_BYTES);
+    detail::DistLib& lib = detail::DistLib::Get();
+    if (lib.get_unique_id(id.data()) != 0) throw std::string("GaussianProcess::GetDistributedId: ") + lib.last_error(nullptr);
+    return id;
+}
+
+template <class TScalarType>
+void GaussianProcess<TScalarType>::SetDistributed(int rank, int world, const void* nccl_id, int Pr, int Pc) {
+    int device = m_DeviceIndex;
+    if (device < 0) {
+        const char* env = std::getenv("GPRB200_DEVICE");
+        device = env ? std::atoi(env) : 0;
+    }
+    m_Dist.reset(new detail::DistModel(device, rank, world, nccl_id, Pr, Pc));
+    m_Initialized = false;
+}
+
+// ComputeRegressionVectors over the GPUs of the grid (SetDistributed): alpha = (K + sigma^2 I)^-1 Y by the block-cyclic
+// Cholesky of libgprb200_dist.so; this rank then holds alpha on the host and on its own GPU, installed like a loaded
+// model (no local factor: a credible interval asked for later factors K on this GPU alone, if it fits).
+template <class TScalarType>
+void GaussianProcess<TScalarType>::ComputeRegressionVectorsDistributed() {
+    detail::DistLib& lib = detail::DistLib::Get();
+    const size_t N = m_SampleVectors.size(), d = m_InputDimension, M = m_OutputDimension;
+    std::vector<int32_t> ops;
+    std::vector<double> params;
+    m_Kernel->Lower(ops, params);
+    std::vector<double> X(N * d), Y(N * M), A(N * M);
+    for (size_t i = 0; i < N; ++i) {
+        for (size_t k = 0; k < d; ++k) X[i * d + k] = m_SampleVectors[i][k];
+        for (size_t k = 0; k < M; ++k) Y[i * M + k] = m_LabelVectors[i][k];
+    }
+    if (lib.set_kernel(m_Dist->d, ops.data(), (int)ops.size(), params.data(), (int)params.size()) != 0)
+        throw std::string(lib.last_error(m_Dist->d));
+    const int rc = lib.learn(m_Dist->d, X.data(), (int64_t)N, (int)d, Y.data(), (int64_t)M, (double)m_Sigma, 0, A.data(),
+                             &m_Dist->logdet);
+    if (rc != 0) throw std::string(lib.last_error(m_Dist->d));
+    m_RegressionVectors.resize(N, M);
+    for (size_t i = 0; i < N * M; ++i) m_RegressionVectors.data()[i] = (TScalarType)A[i];
+    detail::DeviceModel& dev = Device();
+    dev.Check(gprb200_set_kernel(dev.h, ops.data(), (int)ops.size(), params.data(), (int)params.size()));
+    dev.sent_ops = ops;
+    dev.sent_params = params;
+    dev.Check(gprb200_set_state(dev.h, X.data(), (int64_t)N, (int)d, Y.data(), A.data(), (int64_t)M, nullptr, (double)m_Sigma));
+    dev.sent_sigma = (double)m_Sigma;
+    m_TrainDirty = false;
+    m_AlphaMirrored = true;
+    m_CoreMirrored = false;
+    m_CoreMatrix.resize(0, 0);
+    m_CoreSize = m_EfficientStorage ? 0 : (unsigned)N;
+}
+
 // reference :642-672 — Gram + noise, factor, alpha; C is not formed here (see MirrorCoreMatrix)
 template <class TScalarType>
 void GaussianProcess<TScalarType>::ComputeRegressionVectors() {
+    if (m_Dist) {
+        ComputeRegressionVectorsDistributed();
+        return;
+    }
     const size_t N0 = m_SampleVectors.size(), M0 = m_OutputDimension;
     if (std::is_same<TScalarType, double>::value && m_TrainDirty && N0 * M0 * sizeof(double) >= (size_t(64) << 20)) {
         // large label matrix: upload and solve overlapped over column blocks, straight from the AddSample storage

@@ -255,6 +255,51 @@ int main() {
             back->Load("/tmp/gprb200_T8");
             EXPECT(std::fabs(back->Predict(xs)[probe] - yb[probe]) < 1e-13, "T8 Save / Load of the large model");
         }
+        // ---- T9: SetDistributed (world 1: the block-cyclic library's whole code path on one GPU, no exchange) ----------
+        {
+            const unsigned N = 1500;
+            // (GetKernel consumes its argument, as the reference's does: one string per call)
+            std::string ks = "SumKernel(GaussianKernel(1.3,1,),WhiteKernel(0.2,))", ks2 = ks, kg = "GaussianKernel(1.3,1,)";
+            GP::Pointer dist(new GP(KernelFactory<double>::GetKernel(ks)));
+            GP::Pointer plain(new GP(KernelFactory<double>::GetKernel(ks2)));
+            dist->SetSigma(0.5);
+            plain->SetSigma(0.5);
+            for (unsigned i = 0; i < N; ++i) {
+                Vec x(3), y(2);
+                x[0] = std::sin(0.37 * i);
+                x[1] = std::cos(0.11 * i * i);
+                x[2] = std::sin(0.05 * i) * std::cos(0.3 * i);
+                y[0] = std::sin(2 * x[0]) + 0.3 * x[1];
+                y[1] = x[2] * x[0];
+                dist->AddSample(x, y);
+                plain->AddSample(x, y);
+            }
+            dist->SetDistributed(0, 1, nullptr);
+            dist->Initialize();
+            plain->Initialize();
+            Vec xs(3);
+            xs[0] = 0.2;
+            xs[1] = -0.1;
+            xs[2] = 0.05;
+            const Vec a = dist->Predict(xs), b = plain->Predict(xs);
+            EXPECT((a - b).norm() <= 1e-11 * (1 + b.norm()), "T9 SetDistributed: Predict equals the single-GPU model");
+            EXPECT(std::fabs(dist->GetCredibleInterval(xs) - plain->GetCredibleInterval(xs)) <= 1e-10,
+                   "T9 SetDistributed: credible interval (factors locally on demand)");
+            bool threw = false;
+            try {
+                GP::Pointer bad(new GP(KernelFactory<double>::GetKernel(kg)));
+                bad->SetSigma(0);
+                Vec x(1), y(1);
+                x[0] = 0.5;
+                y[0] = 1;
+                for (int i = 0; i < 300; ++i) bad->AddSample(x, y);     // 300 identical samples, no noise: singular
+                bad->SetDistributed(0, 1, nullptr);
+                bad->Initialize();
+            } catch (std::string& s) {
+                threw = s.find("positive definite") != std::string::npos;
+            }
+            EXPECT(threw, "T9 SetDistributed: a singular kernel matrix throws the INFO message");
+        }
     } catch (std::string& s) {
         std::cout << "[failed] exception: " << s << std::endl;
         return -1;

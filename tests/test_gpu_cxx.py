@@ -79,3 +79,15 @@ def test_reference_test_program_passes_against_this_library(exe):
             return
         time.sleep(1.2)
     assert rc == 0 and "[failed]" not in out, out[-4000:]
+
+
+def test_cxx_distributed_initialize_on_two_gpus():
+    """tests/cxx/dist_learn_demo.cpp: GaussianProcess::SetDistributed + Initialize() from plain C++, one forked process per
+    GPU, NCCL id made by the parent; needs two GPUs (the one-rank form is gp_device_test T9)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    exe = os.path.join(ROOT, "tests", "cxx", "bin", "dist_learn_demo")
+    assert os.path.exists(exe), "tests/cxx/bin/dist_learn_demo missing: run __graft_entry__.build()"
+    rc, out = _run(exe)
+    assert rc == 0 and "[failed]" not in out and "dist_learn_demo: [passed]" in out, out[-4000:]
