@@ -25,6 +25,8 @@ _PROTOS = {
     "gprb200_dist_learn": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_double, C.c_int64,
                                      C.c_void_p, C.POINTER(C.c_double)]),
     "gprb200_dist_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "gprb200_dist_plan": (C.c_int, [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_int64]),
     "gprb200_dist_phase_ms": (C.c_double, [C.c_void_p, C.c_int]),
     "gprb200_dist_counter": (C.c_double, [C.c_void_p, C.c_int]),
 }
@@ -70,6 +72,23 @@ def exchange_id(group=None):
     box = [get_unique_id() if dist.get_rank(group) == 0 else None]
     dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     return box[0]
+
+
+def plan(N, nb, Pr, Pc, rank, mirror_rows=True, mirror_cols=False):
+    """Host-only layout of one rank (gprb200_dist_plan): dict with H, Wtot, bytes, flops, row / column offsets, stair."""
+    lib = load_dist_library()
+    summary = np.zeros(6)
+    nblk = (N + nb - 1) // nb
+    rows, cols = np.full(nblk, -2, dtype=np.int32), np.full(nblk, -2, dtype=np.int32)
+    rc = lib.gprb200_dist_plan(N, nb, Pr, Pc, rank, int(mirror_rows), int(mirror_cols), summary.ctypes.data, rows.ctypes.data,
+                               cols.ctypes.data, None, 0)
+    if rc != 0:
+        raise GprError(rc, lib.gprb200_dist_last_error(None).decode())
+    stair = np.zeros(int(summary[5]), dtype=np.int32)
+    lib.gprb200_dist_plan(N, nb, Pr, Pc, rank, int(mirror_rows), int(mirror_cols), summary.ctypes.data, None, None,
+                          stair.ctypes.data, stair.size)
+    return {"H": int(summary[0]), "Wtot": int(summary[1]), "bytes": summary[2], "flops": summary[3], "row_offset": rows,
+            "col_offset": cols, "stair": stair}
 
 
 def _arr(a):

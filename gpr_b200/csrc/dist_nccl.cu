@@ -176,13 +176,9 @@ inline int bcast(gprb200_dist* d, double* buf, int64_t count, int root, ncclComm
 
 namespace {
 
-// ---- ownership maps and device buffers ----------------------------------------------------------------------------
-int setup_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb) {
-    if (d->P.N == N && d->P.nb == nb && d->P.dim == dim && d->P.dX) {   // same shape as the last learn: keep the buffers
-        d->P.factored = false;
-        return 0;
-    }
-    release_problem(d);
+// Host-only part of the set-up: who owns what, where it sits in the local matrix, and the staircase table. No CUDA call
+// (gprb200_dist_plan runs it without a GPU; tests/test_dist_plan.py).
+void plan_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb, std::vector<int>* stair_out) {
     Problem& P = d->P;
     P.N = N; P.nb = nb; P.dim = dim; P.nblk = (N + nb - 1) / nb;
     P.hgt.resize(P.nblk); P.roff.assign(P.nblk, -1);
@@ -196,18 +192,48 @@ int setup_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb) {
     P.coff.assign(P.nblk, -1);
     for (int64_t j : P.mine) { P.coff[j] = P.Wtot; P.Wtot += P.hgt[j]; }
     P.LDA = (P.Wtot + 1) / 2 * 2;
-    RK(dmalloc(d, (void**)&P.A, (size_t)std::max<int64_t>(P.H, 1) * std::max<int64_t>(P.LDA, 2) * 8));
-    std::vector<int> stair((size_t)(P.Wtot + 63) / 64 + 1, (int)P.H);
+    std::vector<int>& stair = *stair_out;
+    stair.assign((size_t)(P.Wtot + 63) / 64 + 1, (int)P.H);
     for (int64_t j : P.mine) {
         int64_t off, first;
         first_at_or_after(d, j, &off, &first);
         P.off[j] = off; P.first[j] = first;
         if (first < 0) continue;
         P.ld[j] = P.LDA;
-        P.cols[j] = P.A + off * P.LDA + P.coff[j];
         // columns [c, c + 64) of the diagonal block need the rows from c on (lower triangle), the others the whole block row
         for (int64_t c = 0; c < P.hgt[j]; c += 64) stair[(size_t)(P.coff[j] + c) / 64] = (int)(off + (first == j ? c : 0));
-        if (first == j) RK(dmalloc(d, (void**)&P.invl[j], (size_t)((P.hgt[j] + 127) / 128) * 128 * 128 * 8));
+    }
+}
+
+// flop this rank's GEMMs execute in one factorisation (the same accounting as the n_flop counter of a real run)
+double plan_flops(gprb200_dist* d) {
+    Problem& P = d->P;
+    double f = 0.0;
+    for (int64_t k = 0; k + 1 < P.nblk; ++k) {
+        int64_t o1, first;
+        first_at_or_after(d, k + 1, &o1, &first);
+        if (colof(d, k) == d->pc && first >= 0) f += 1.0 * (P.H - o1) * P.hgt[k] * (P.hgt[k] + 64);
+        for (int64_t j : P.mine)
+            if (j > k && P.first[j] >= 0) f += 2.0 * (P.H - P.off[j]) * P.hgt[j] * P.nb;
+    }
+    return f;
+}
+
+// ---- ownership maps and device buffers ----------------------------------------------------------------------------
+int setup_problem(gprb200_dist* d, int64_t N, int dim, int64_t nb) {
+    if (d->P.N == N && d->P.nb == nb && d->P.dim == dim && d->P.dX) {   // same shape as the last learn: keep the buffers
+        d->P.factored = false;
+        return 0;
+    }
+    release_problem(d);
+    Problem& P = d->P;
+    std::vector<int> stair;
+    plan_problem(d, N, dim, nb, &stair);
+    RK(dmalloc(d, (void**)&P.A, (size_t)std::max<int64_t>(P.H, 1) * std::max<int64_t>(P.LDA, 2) * 8));
+    for (int64_t j : P.mine) {
+        if (P.first[j] < 0) continue;
+        P.cols[j] = P.A + P.off[j] * P.LDA + P.coff[j];
+        if (P.first[j] == j) RK(dmalloc(d, (void**)&P.invl[j], (size_t)((P.hgt[j] + 127) / 128) * 128 * 128 * 8));
     }
     RK(dmalloc(d, (void**)&P.stair, stair.size() * sizeof(int)));
     CK(cudaMemcpyAsync(P.stair, stair.data(), stair.size() * sizeof(int), cudaMemcpyHostToDevice, d->sm));
@@ -737,6 +763,26 @@ int gprb200_dist_solve(gprb200_dist_handle d, const double* Y, int64_t M, double
     RK(solve(d, Y, M, alpha));
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, d->t2, d->t3)); d->ms[2] = ms;
+    return 0;
+}
+
+int gprb200_dist_plan(int64_t N, int64_t nb, int Pr, int Pc, int rank, int mirror_rows, int mirror_cols, double* summary,
+                      int32_t* row_owned, int32_t* col_owned, int32_t* stair, int64_t stair_len) {
+    gprb200_dist* d = nullptr;
+    if (nb == 0) nb = 1024;
+    if (N < 1 || nb < 128 || nb % 128 != 0 || Pr < 1 || Pc < 1 || rank < 0 || rank >= Pr * Pc || !summary)
+        return fail(d, -2, "gprb200_dist_plan: bad arguments");
+    gprb200_dist t;     // never touches CUDA or NCCL
+    t.Pr = Pr; t.Pc = Pc; t.world = Pr * Pc; t.rank = rank; t.pr = rank / Pc; t.pc = rank % Pc;
+    t.mirror_rows = mirror_rows != 0; t.mirror_cols = mirror_cols != 0;
+    std::vector<int> st;
+    plan_problem(&t, N, 1, nb, &st);
+    const Problem& P = t.P;
+    summary[0] = (double)P.H; summary[1] = (double)P.Wtot; summary[2] = 8.0 * (double)std::max<int64_t>(P.H, 1) * (double)std::max<int64_t>(P.LDA, 2);
+    summary[3] = plan_flops(&t); summary[4] = (double)P.nblk; summary[5] = (double)st.size();
+    if (row_owned) for (int64_t i = 0; i < P.nblk; ++i) row_owned[i] = P.roff[i] >= 0 ? (int32_t)P.roff[i] : -1;
+    if (col_owned) for (int64_t j = 0; j < P.nblk; ++j) col_owned[j] = P.coff[j] >= 0 ? (int32_t)P.coff[j] : -1;
+    if (stair) for (int64_t u = 0; u < stair_len && u < (int64_t)st.size(); ++u) stair[u] = st[u];
     return 0;
 }
 

@@ -65,6 +65,15 @@ double gprb200_dist_phase_ms(gprb200_dist_handle d, int which);
  * inside trailing updates, 6 the flop of those updates (factorisation only); 7 / 8: Pr / Pc of the grid in use. */
 double gprb200_dist_counter(gprb200_dist_handle d, int which);
 
+/* Host-only (no GPU, no NCCL call): the layout rank `rank` of a Pr x Pc grid would use for an N x N problem - for capacity
+ * planning and for tests of the ownership logic. summary[6]: 0 stacked rows H, 1 local columns Wtot, 2 bytes of the local
+ * matrix, 3 flop this rank's GEMMs execute in one factorisation (compare N^3 / (3 Pr Pc)), 4 number of block rows,
+ * 5 entries of the staircase table. row_owned / col_owned (nblk ints each, may be NULL): offset of block row i / block
+ * column j in the local matrix, -1 if another rank's. stair (may be NULL): the first stair_len entries of the table
+ * gprb200_gemm_stair_dev gets (first local row needed by each 64 local columns). */
+int gprb200_dist_plan(int64_t N, int64_t nb, int Pr, int Pc, int rank, int mirror_rows, int mirror_cols, double* summary,
+                      int32_t* row_owned, int32_t* col_owned, int32_t* stair, int64_t stair_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,6 +22,8 @@ def test_dist_capi_learn_matches_oracle_and_single_gpu(N, nb, M, kname):
     d.set_kernel(ops_, params)
     alpha, logdet = d.learn(X, Y, 1.0, nb=nb)
     assert d.counters()["launches"] > 0 and d.counters()["collectives"] == 0
+    # the flop the run issued is what the host-only plan (tests/test_dist_plan.py) predicts for this rank
+    assert d.counters()["gemm_flops"] == capi_dist.plan(N, nb, 1, 1, 0)["flops"]
     o = orc.OracleGP(KERNELS[kname], X, Y, 1.0)
     o.learn()
     assert rel_err(alpha, o.alpha) <= 1e-9      # BASELINE.json tolerance on alpha
