@@ -107,7 +107,8 @@ public:
     // Cholesky, NCCL) and every rank keeps the regression vectors, so Predict runs locally on each. nccl_id: the
     // GetDistributedId() bytes of rank 0, carried to the other ranks by the application (MPI_Bcast, a file, ...);
     // world == 1 needs none. Pr = Pc = 0: the library's default grid. libgprb200_dist.so is opened on first use, so
-    // programs that never call this do not need NCCL.
+    // programs that never call this do not need NCCL. The Cholesky factor stays on the grid: operator()(x, y) and
+    // GetCredibleInterval(x) then solve there and are COLLECTIVE (every rank makes the same call and gets the value).
     void SetDistributed(int rank, int world, const void* nccl_id, int Pr = 0, int Pc = 0);
     static std::vector<unsigned char> GetDistributedId();
     // milliseconds of the last Gram / Cholesky / solve / inverse / predict phases (CUDA events)

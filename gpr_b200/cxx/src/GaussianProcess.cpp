@@ -49,6 +49,7 @@ struct DistLib {
     decltype(&gprb200_dist_last_error) last_error = nullptr;
     decltype(&gprb200_dist_set_kernel) set_kernel = nullptr;
     decltype(&gprb200_dist_learn) learn = nullptr;
+    decltype(&gprb200_dist_solve) solve = nullptr;
 
     static DistLib& Get() {
         static DistLib lib;
@@ -66,6 +67,7 @@ struct DistLib {
             lib.last_error = reinterpret_cast<decltype(lib.last_error)>(sym("gprb200_dist_last_error"));
             lib.set_kernel = reinterpret_cast<decltype(lib.set_kernel)>(sym("gprb200_dist_set_kernel"));
             lib.learn = reinterpret_cast<decltype(lib.learn)>(sym("gprb200_dist_learn"));
+            lib.solve = reinterpret_cast<decltype(lib.solve)>(sym("gprb200_dist_solve"));
         }
         return lib;
     }
@@ -406,6 +408,19 @@ TScalarType GaussianProcess<TScalarType>::operator()(const VectorType& x, const 
     const double* px = sx.In(x.data(), m_InputDimension);
     const double* py = sy.In(y.data(), m_InputDimension);
     double cov = 0.0;
+    if (m_Dist) {
+        // the factor lives on the GPU grid, not on this GPU: gp(x, y) = k(x, y) - Kx^T (K + sigma^2 I)^-1 Ky with the solve
+        // on the grid. COLLECTIVE: every rank makes the same call (each gets the value).
+        detail::DistLib& lib = detail::DistLib::Get();
+        const size_t N = m_SampleVectors.size();
+        std::vector<double> Kx(N), Ky(N), S(N);
+        dev.Check(gprb200_kernel_vector(dev.h, px, 1, Kx.data()));
+        dev.Check(gprb200_kernel_vector(dev.h, py, 1, Ky.data()));
+        if (lib.solve(m_Dist->d, Ky.data(), 1, S.data()) != 0) throw std::string(lib.last_error(m_Dist->d));
+        long double acc = 0;
+        for (size_t i = 0; i < N; ++i) acc += (long double)Kx[i] * S[i];
+        return static_cast<TScalarType>((double)(*m_Kernel)(x, y) - (double)acc);
+    }
     dev.Check(gprb200_posterior_cov(dev.h, px, py, 1, &cov));
     return static_cast<TScalarType>(cov);
 }

@@ -46,14 +46,16 @@ static int run_rank(int rank, int world, const std::vector<unsigned char>& id, u
         xs[1] = -0.1;
         xs[2] = 0.05;
         const Vec a = gp->Predict(xs);
+        const double ci = gp->GetCredibleInterval(xs);      // collective: every rank asks
         if (rank == 0) {
             GP::Pointer plain = make_model(N);
             plain->SetDevice(0);
             const Vec b = plain->Predict(xs);
-            const bool ok = (a - b).norm() <= 1e-10 * (1 + b.norm());
+            const double ci1 = plain->GetCredibleInterval(xs);
+            const bool ok = (a - b).norm() <= 1e-10 * (1 + b.norm()) && std::fabs(ci - ci1) <= 1e-9;
             std::cout << (ok ? "[passed]" : "[failed]") << " " << world << " ranks, N = " << N
-                      << ": Predict after the distributed Initialize equals the single-GPU model (|diff| = " << (a - b).norm()
-                      << ")" << std::endl;
+                      << ": Predict and GetCredibleInterval after the distributed Initialize equal the single-GPU model (|diff| = "
+                      << (a - b).norm() << ", " << std::fabs(ci - ci1) << ")" << std::endl;
             return ok ? 0 : 1;
         }
         return 0;

@@ -284,7 +284,7 @@ int main() {
             const Vec a = dist->Predict(xs), b = plain->Predict(xs);
             EXPECT((a - b).norm() <= 1e-11 * (1 + b.norm()), "T9 SetDistributed: Predict equals the single-GPU model");
             EXPECT(std::fabs(dist->GetCredibleInterval(xs) - plain->GetCredibleInterval(xs)) <= 1e-10,
-                   "T9 SetDistributed: credible interval (factors locally on demand)");
+                   "T9 SetDistributed: credible interval through the solve on the grid");
             bool threw = false;
             try {
                 GP::Pointer bad(new GP(KernelFactory<double>::GetKernel(kg)));
