@@ -58,6 +58,8 @@ struct Problem {
     long long* dflag = nullptr;
     double* dsum = nullptr;
     std::vector<void*> allocs;
+    std::vector<void*> ws;                   // workspace of solve() for right-hand sides of leading dimension ws_ld
+    int64_t ws_ld = 0;
     std::vector<cudaEvent_t> ev_main, ev_panel, ev_start;
     bool factored = false;
     double logdet = 0.0;
@@ -138,6 +140,7 @@ int release_problem(gprb200_dist* d) {
     Problem& P = d->P;
     cudaDeviceSynchronize();
     for (void* p : P.allocs) cudaFree(p);
+    for (void* p : P.ws) cudaFree(p);
     for (cudaEvent_t e : P.ev_main) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : P.ev_panel) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : P.ev_start) if (e) cudaEventDestroy(e);
@@ -358,9 +361,11 @@ int distribute(gprb200_dist* d, int64_t k) {
         pos[r2] += P.hgt[*it];
     }
     NK(ncclGroupStart());
-    for (int r2 = 0; r2 < d->Pr; ++r2)
-        if (total[r2] > 0) RK(bcast(d, P.colbuf[k % 2][r2], total[r2] * nb, r2, d->col_comm, d->sp));
+    int grc = 0;    // an error inside the group must not leave it open
+    for (int r2 = 0; r2 < d->Pr && grc == 0; ++r2)
+        if (total[r2] > 0) grc = bcast(d, P.colbuf[k % 2][r2], total[r2] * nb, r2, d->col_comm, d->sp);
     NK(ncclGroupEnd());
+    if (grc) return grc;
     std::fill(pos.begin(), pos.end(), 0);
     for (auto it = jbeg; it != P.mine.end(); ++it) {
         const int r2 = rowof(d, *it);
@@ -485,26 +490,28 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
     cudaStream_t st = d->sm;
     gprb200_handle h = d->hm;
     double *y = nullptr, *acc = nullptr, *out = nullptr, *msg[2] = {nullptr, nullptr}, *zown = nullptr;
-    std::vector<void*> tmp;
-    auto talloc = [&](double** p, size_t n) -> int {
-        CK(cudaMalloc((void**)p, std::max<size_t>(n * 8, 256)));
-        tmp.push_back(*p);
-        CK(cudaMemsetAsync(*p, 0, std::max<size_t>(n * 8, 256), st));
-        return 0;
-    };
-    auto tfree = [&]() { for (void* p : tmp) cudaFree(p); };
-    int rc = 0;
     int64_t ndiag = 0;
     std::vector<int64_t> zoff(nblk, -1);
     for (int64_t k = 0; k < nblk; ++k)
         if (rowof(d, k) == d->pr && colof(d, k) == d->pc) { zoff[k] = ndiag; ndiag += P.hgt[k]; }
     double* stage = nullptr;     // contiguous N x M image of the host array (a pitched copy of 8-byte rows crawls)
-    if ((rc = talloc(&y, (size_t)N * ld)) || (rc = talloc(&out, (size_t)N * ld)) || (rc = talloc(&stage, (size_t)N * M)) ||
-        (rc = talloc(&acc, (size_t)std::max<int64_t>(P.H, 1) * ld)) || (rc = talloc(&msg[0], (size_t)nb * ld)) ||
-        (rc = talloc(&msg[1], (size_t)nb * ld)) || (rc = talloc(&zown, (size_t)std::max<int64_t>(ndiag, 1) * ld))) {
-        tfree();
-        return rc;
+    // the workspace is kept for the next call with the same number of columns (one interval per call: GetCredibleInterval)
+    const size_t sizes[7] = {(size_t)N * ld, (size_t)N * ld, (size_t)N * ld /* stage: N x M, M <= ld */, (size_t)std::max<int64_t>(P.H, 1) * ld, (size_t)nb * ld,
+                             (size_t)nb * ld, (size_t)std::max<int64_t>(ndiag, 1) * ld};
+    if (P.ws_ld != ld || P.ws.size() != 7) {
+        for (void* p : P.ws) cudaFree(p);
+        P.ws.clear();
+        P.ws_ld = 0;
+        for (int i = 0; i < 7; ++i) {
+            void* p = nullptr;
+            CK(cudaMalloc(&p, std::max<size_t>(sizes[i] * 8, 256)));
+            P.ws.push_back(p);
+        }
+        P.ws_ld = ld;
     }
+    y = (double*)P.ws[0]; out = (double*)P.ws[1]; stage = (double*)P.ws[2]; acc = (double*)P.ws[3];
+    msg[0] = (double*)P.ws[4]; msg[1] = (double*)P.ws[5]; zown = (double*)P.ws[6];
+    for (int i = 0; i < 7; ++i) CK(cudaMemsetAsync(P.ws[i], 0, std::max<size_t>(sizes[i] * 8, 256), st));
     auto body = [&]() -> int {
         if (ld == M) {
             CK(cudaMemcpyAsync(y, Yhost, (size_t)N * M * 8, cudaMemcpyHostToDevice, st));
@@ -590,9 +597,8 @@ int solve(gprb200_dist* d, const double* Yhost, int64_t M, double* alpha_host) {
         CK(cudaStreamSynchronize(st));
         return 0;
     };
-    rc = body();
+    const int rc = body();
     cudaStreamSynchronize(st);
-    tfree();
     return rc;
 }
 

@@ -7,6 +7,7 @@
 #include <fstream>
 #include <iomanip>
 #include <limits>
+#include <mutex>
 #include <sstream>
 #include <type_traits>
 #include <dlfcn.h>
@@ -53,6 +54,8 @@ struct DistLib {
 
     static DistLib& Get() {
         static DistLib lib;
+        static std::mutex guard;    // ranks may be threads of one process
+        std::lock_guard<std::mutex> lock(guard);
         if (!lib.so) {
             lib.so = ::dlopen("libgprb200_dist.so", RTLD_NOW | RTLD_GLOBAL);   // found through libgplib.so's RUNPATH
             if (!lib.so) throw std::string("GaussianProcess::SetDistributed: cannot open libgprb200_dist.so: ") + ::dlerror();
