@@ -604,12 +604,15 @@ def run_predict_ci(args, env, N=16384, d=8, T=4096):
     g.learn()
     b, e = gd.column_shard(T, rank, world)
     g.credible_interval(Xs[:64], gather=False)
-    env["barrier"]()
-    t0 = time.perf_counter()
-    mean = g.predict(Xs[b:e])                      # this rank's output columns (may be none when M < g)
-    ci = g.credible_interval(Xs, gather=False)     # this rank's test points
-    torch.cuda.synchronize()
-    batch_ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3)
+    batch_ms = None
+    for _ in range(3):      # a 10-30 ms host-timed region, max over ranks: the best of three passes
+        env["barrier"]()
+        t0 = time.perf_counter()
+        mean = g.predict(Xs[b:e])                      # this rank's output columns (may be none when M < g)
+        ci = g.credible_interval(Xs, gather=False)     # this rank's test points
+        torch.cuda.synchronize()
+        ms = env["max_over_ranks"]((time.perf_counter() - t0) * 1e3)
+        batch_ms = ms if batch_ms is None else min(batch_ms, ms)
     one_ms = None
     if g.shard[1] > g.shard[0]:
         for i in range(3):
