@@ -58,6 +58,8 @@ class GaussianProcess:
         self._core = None        # host mirror of m_CoreMatrix (lazy)
         self._core_size = 0      # what m_CoreMatrix.diagonalSize() would be
         self._loaded = False
+        self._device = device
+        self._dist = None        # capi_dist.DistHandle of this rank after SetDistributed
 
     # ---- helpers -----------------------------------------------------------------------------
     def _sync_kernel(self):
@@ -105,6 +107,41 @@ class GaussianProcess:
         self.m_Initialized = False
         self._train_dirty = True
 
+    def SetDistributed(self, rank, world, unique_id=None, grid=None):
+        """ONE model over several GPUs (mirror of gpr::GaussianProcess<T>::SetDistributed; not in the reference): call on
+        every rank before Initialize(). unique_id: capi_dist.get_unique_id() of rank 0 (capi_dist.exchange_id() carries it
+        over a torch.distributed group). Initialize() then factors on the grid; Predict runs locally, __call__ and
+        GetCredibleInterval solve on the grid and are collective."""
+        from . import capi_dist
+        self._dist = capi_dist.DistHandle(self._device, rank, world, unique_id, grid)
+        self.m_Initialized = False
+
+    def _kernel_value(self, x, y):
+        """k(x, y) on the device (the Python kernel classes carry parameters only): a one-sample model whose kernel vector
+        at x is the value."""
+        if getattr(self, "_pair_h", None) is None:
+            self._pair_h = Handle(self._device)
+        ops, params = self.m_Kernel.lower()
+        self._pair_h.set_kernel(ops, params)
+        self._pair_h.set_train(y[None, :], np.zeros((1, 1)), 0.0)
+        return float(self._pair_h.kernel_vector(x[None, :])[0, 0])
+
+    def _initialize_distributed(self):
+        ops, params = self.m_Kernel.lower()
+        X = np.stack(self.m_SampleVectors).astype(np.float64)
+        Y = np.stack(self.m_LabelVectors).astype(np.float64)
+        self._dist.set_kernel(ops, params)
+        alpha, self._dist_logdet = self._dist.learn(X, Y, self.m_Sigma)
+        self._h.set_kernel(ops, params)
+        self._sent_kernel = (tuple(ops), tuple(params))
+        self._h.set_state(X, Y, alpha, None, self.m_Sigma)      # alpha on this rank's GPU, like a loaded model
+        self._train_dirty = False
+        self._alpha = alpha
+        self._core = None
+        self._core_size = 0 if self.m_EfficientStorage else len(self.m_SampleVectors)
+        self._loaded = False
+        self.m_Initialized = True
+
     def Initialize(self):  # lib/GaussianProcess.cpp:118-130
         if self.m_Initialized:
             return
@@ -112,6 +149,8 @@ class GaussianProcess:
             raise GprError(-2, "GaussianProcess::Initialize: no input samples defined during initialization")
         if not self.m_LabelVectors:
             raise GprError(-2, "GaussianProcess::Initialize: no ouput labels defined during initialization")
+        if self._dist is not None:
+            return self._initialize_distributed()
         self._sync_kernel()
         self._sync_train()
         self._h.set_sigma(self.m_Sigma)
@@ -153,6 +192,10 @@ class GaussianProcess:
         self._sync_kernel()
         if self._core_size == 0:
             self._core_size = len(self.m_SampleVectors)  # the reference rebuilds m_CoreMatrix here (:95-97)
+        if self._dist is not None:      # the factor lives on the grid: k(x, y) - Kx^T (K + s^2 I)^-1 Ky, collective
+            Kx, Ky = self._h.kernel_vector(x[None, :])[0], self._h.kernel_vector(y[None, :])[0]
+            S = self._dist.solve(Ky[:, None])[:, 0]
+            return float(self._kernel_value(x, y) - np.dot(Kx.astype(np.longdouble), S.astype(np.longdouble)))
         return float(self._h.posterior_cov(x[None, :], y[None, :])[0])
 
     def GetCredibleInterval(self, x):  # lib/GaussianProcess.cpp:103-114

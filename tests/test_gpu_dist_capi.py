@@ -76,3 +76,24 @@ def test_dist_capi_argument_errors():
     with pytest.raises(gpr_b200.GprError, match="multiple of 128"):
         d.learn(X, Y, 1.0, nb=200)
     d.close()
+
+
+def test_python_mirror_set_distributed_matches_the_plain_model():
+    """gpr_b200.GaussianProcess.SetDistributed (mirror of the C++ host class): Initialize on the (one-rank) grid, Predict
+    locally, posterior covariance / credible interval through the solve on the grid."""
+    import gpr_b200
+    X, Y = make_problem(900, 3, 2, seed=21)
+    gps = []
+    for dist_on in (True, False):
+        gp = gpr_b200.GaussianProcess(gpr_b200.KernelFactory.GetKernel(KERNELS["sum3"]))
+        gp.SetSigma(0.6)
+        for x, y in zip(X, Y):
+            gp.AddSample(x, y)
+        if dist_on:
+            gp.SetDistributed(0, 1)
+        gp.Initialize()
+        gps.append(gp)
+    xs, ys = X[5] + 0.03, X[9] - 0.02
+    assert rel_err(gps[0].Predict(xs), gps[1].Predict(xs)) <= 1e-11
+    assert abs(gps[0](xs, ys) - gps[1](xs, ys)) <= 1e-11
+    assert abs(gps[0].GetCredibleInterval(xs) - gps[1].GetCredibleInterval(xs)) <= 1e-10
