@@ -36,6 +36,26 @@ def main():
     for kv in os.environ.get("DIST_OPTS", "").split(","):
         if "=" in kv:
             d.set_option(kv.split("=")[0], int(kv.split("=")[1]))
+    if os.environ.get("DIST_BAD"):
+        # a duplicated sample and no noise: every rank must come back with the SAME LAPACK-style INFO and nobody may hang
+        Xb = X.copy()
+        dup = N // 2 + 3
+        Xb[dup] = Xb[7]
+        opsb, paramsb = gpr_b200.KernelFactory.GetKernel("GaussianKernel(2,1,)").lower()
+        d.set_kernel(opsb, paramsb)
+        code = 0
+        try:
+            d.learn(Xb, Y, 0.0, nb=nb)
+        except gpr_b200.GprError as e:
+            code = e.code
+        codes = [None] * world
+        if world > 1:
+            dist.all_gather_object(codes, code)
+        else:
+            codes = [code]
+        if rank == 0:
+            print(json.dumps({"non_spd_info_per_rank": codes, "expected": dup + 1, "ok": all(c == dup + 1 for c in codes)}), flush=True)
+        d.set_kernel(ops_, params)
     out = {}
     for it in range(reps):
         if world > 1:
