@@ -372,7 +372,27 @@ void GaussianProcess<TScalarType>::PredictBatch(const MatrixType& Xs, MatrixType
     const double* px = sx.In(Xs.data(), T * m_InputDimension);
     double* pm = sm.Out(mean.data(), T * m_OutputDimension);
     double* pc = ci ? sc.Out(ci->data(), T) : nullptr;
-    dev.Check(gprb200_predict(dev.h, px, (int64_t)T, pm, pc));
+    if (ci && m_Dist) {
+        // the factor lives on the GPU grid: the T kernel vectors are T right-hand sides of ONE distributed solve
+        // (collective: every rank makes the same call), ci_t = 2 sqrt(max(0, k(x_t, x_t) - Kx_t^T (K + s^2 I)^-1 Kx_t))
+        dev.Check(gprb200_predict(dev.h, px, (int64_t)T, pm, nullptr));
+        detail::DistLib& lib = detail::DistLib::Get();
+        const size_t N = m_SampleVectors.size();
+        std::vector<double> Kx(T * N), Kt(N * T), S(N * T);
+        dev.Check(gprb200_kernel_vector(dev.h, px, (int64_t)T, Kx.data()));
+        for (size_t t = 0; t < T; ++t)
+            for (size_t i = 0; i < N; ++i) Kt[i * T + t] = Kx[t * N + i];
+        if (lib.solve(m_Dist->d, Kt.data(), (int64_t)T, S.data()) != 0) throw std::string(lib.last_error(m_Dist->d));
+        for (size_t t = 0; t < T; ++t) {
+            long double acc = 0;
+            for (size_t i = 0; i < N; ++i) acc += (long double)Kt[i * T + t] * S[i * T + t];
+            VectorType xt = Xs.row(t).transpose();
+            const double c = (double)(*m_Kernel)(xt, xt) - (double)acc;
+            pc[t] = c > 0 ? 2.0 * std::sqrt(c) : 0.0;
+        }
+    } else {
+        dev.Check(gprb200_predict(dev.h, px, (int64_t)T, pm, pc));
+    }
     sm.Finish(mean.data(), T * m_OutputDimension);
     if (ci) sc.Finish(ci->data(), T);
     if (ci && m_CoreSize == 0) m_CoreSize = m_SampleVectors.size();

@@ -285,6 +285,19 @@ int main() {
             EXPECT((a - b).norm() <= 1e-11 * (1 + b.norm()), "T9 SetDistributed: Predict equals the single-GPU model");
             EXPECT(std::fabs(dist->GetCredibleInterval(xs) - plain->GetCredibleInterval(xs)) <= 1e-10,
                    "T9 SetDistributed: credible interval through the solve on the grid");
+            {   // batch of test points: T right-hand sides of one distributed solve
+                Mat Xb(5, 3), mb, mp;
+                for (int t = 0; t < 5; ++t) {
+                    Xb(t, 0) = 0.1 * t - 0.2;
+                    Xb(t, 1) = 0.3 - 0.05 * t;
+                    Xb(t, 2) = 0.02 * t * t;
+                }
+                Vec cb, cp;
+                dist->PredictBatch(Xb, mb, &cb);
+                plain->PredictBatch(Xb, mp, &cp);
+                EXPECT((mb - mp).norm() <= 1e-11 * (1 + mp.norm()) && (cb - cp).norm() <= 1e-9,
+                       "T9 SetDistributed: PredictBatch with intervals (one solve with T right-hand sides on the grid)");
+            }
             bool threw = false;
             try {
                 GP::Pointer bad(new GP(KernelFactory<double>::GetKernel(kg)));
