@@ -190,8 +190,11 @@ class BlockCyclicGP:
     Replaces, for large N, the reference's single-process InvertKernelMatrix + C * Y
     (lib/GaussianProcess.cpp:531-560, :661)."""
 
-    def __init__(self, ops, N, nb=1024, grid=None, group=None):
+    def __init__(self, ops, N, nb=1024, grid=None, group=None, mirror_rows=False, mirror_cols=False):
         self.ops = ops
+        # block-to-grid maps: plain cyclic, or mirrored (0 1 .. P-1 P-1 .. 1 0), which evens out the lower triangle's bias
+        # towards high grid rows; libgprb200_dist.so mirrors its row map by default (DESIGN.md section 5)
+        self.mirror_rows, self.mirror_cols = bool(mirror_rows), bool(mirror_cols)
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -205,14 +208,14 @@ class BlockCyclicGP:
         self.pr, self.pc = divmod(self.rank, self.Pc)
         self.nblk = (self.N + self.nb - 1) // self.nb
         self.hgt = [min(self.nb, self.N - i * self.nb) for i in range(self.nblk)]   # block heights = widths
-        self.myrows = [i for i in range(self.nblk) if i % self.Pr == self.pr]       # block rows stacked in every local panel
+        self.myrows = [i for i in range(self.nblk) if self._rowof(i) == self.pr]       # block rows stacked in every local panel
         self.roff = {}
         o = 0
         for i in self.myrows:
             self.roff[i] = o
             o += self.hgt[i]
         self.H = o
-        self.mine = [j for j in range(self.nblk) if j % self.Pc == self.pc]         # owned block columns
+        self.mine = [j for j in range(self.nblk) if self._colof(j) == self.pc]         # owned block columns
         self._ranks = list(range(self.world))
         if group is not None and self.world > 1:
             self._ranks = dist.get_process_group_ranks(group)
@@ -226,6 +229,19 @@ class BlockCyclicGP:
         self.stats = {"bcast_bytes": 0, "gemm_flops": 0.0, "collectives": 0}
 
     # -- grid helpers -----------------------------------------------------------------------------------------------
+    @staticmethod
+    def _cyc(i, P, mirror):
+        if not mirror or P == 1:
+            return i % P
+        t = i % (2 * P)
+        return t if t < P else 2 * P - 1 - t
+
+    def _rowof(self, i):
+        return self._cyc(i, self.Pr, self.mirror_rows)
+
+    def _colof(self, j):
+        return self._cyc(j, self.Pc, self.mirror_cols)
+
     def _grank(self, r, c):
         return self._ranks[r * self.Pc + c]
 
@@ -282,7 +298,7 @@ class BlockCyclicGP:
             self._bufs = {"row": [ops.empty(max(self.H, 1), nb) for _ in range(2)], "W": [ops.empty(nb, nb) for _ in range(2)],
                           "eye": ops.eye(nb), "col": None}
             if self.Pr > 1:
-                cnt = [sum(self.hgt[j] for j in self.mine if j % self.Pr == r2) for r2 in range(self.Pr)]
+                cnt = [sum(self.hgt[j] for j in self.mine if self._rowof(j) == r2) for r2 in range(self.Pr)]
                 self._bufs["col"] = [[ops.empty(max(c, 1), nb) for c in cnt] for _ in range(2)]
             self.info = ops.new_info()
 
@@ -311,10 +327,10 @@ class BlockCyclicGP:
         """Ranks of grid column k mod Pc, panel stream: L_kk, W = inv(L_kk) down the column, X_i = A_ik W^T for the
         owned rows below; X is left in the row-panel buffer k % 2 AND in cols[k] (the factor, needed by solve)."""
         ops, nb = self.ops, self.nb
-        if k % self.Pc != self.pc:
+        if self._colof(k) != self.pc:
             return
         w = self.hgt[k]
-        diag = (k % self.Pr == self.pr)
+        diag = (self._rowof(k) == self.pr)
         if diag:
             blk = self.cols[k][:w, :w]
             ops.potrf_block(blk, self.invl[k], k * nb, self.info, "panel")
@@ -325,7 +341,7 @@ class BlockCyclicGP:
             W.copy_(self._bufs["eye"])
             ops.trsm(blk, self.invl[k], W, False, "panel")
         if self.Pr > 1:
-            self._bcast(W, self._grank(k % self.Pr, self.pc), self.col_group)
+            self._bcast(W, self._grank(self._rowof(k), self.pc), self.col_group)
         o1, first = self._first_row_at_or_after(k + 1)
         if first is None:
             return
@@ -343,10 +359,10 @@ class BlockCyclicGP:
         o1, first = self._first_row_at_or_after(k + 1)
         X = self._bufs["row"][k % 2][:self.H - o1]
         if self.Pc > 1 and first is not None:
-            self._bcast(X, self._grank(self.pr, k % self.Pc), self.row_group)
+            self._bcast(X, self._grank(self.pr, self._colof(k)), self.row_group)
         if self.Pr > 1:
             for r2 in range(self.Pr):
-                blocks = [j for j in self.mine if j > k and j % self.Pr == r2]
+                blocks = [j for j in self.mine if j > k and self._rowof(j) == r2]
                 if not blocks:
                     continue
                 buf = self._bufs["col"][k % 2][r2][:sum(self.hgt[j] for j in blocks)]
@@ -362,8 +378,8 @@ class BlockCyclicGP:
         if self.Pr == 1:
             o1, _ = self._first_row_at_or_after(k + 1)
             return self._bufs["row"][k % 2][self.roff[j] - o1:self.roff[j] - o1 + self.hgt[j]]
-        r2 = j % self.Pr
-        pos = sum(self.hgt[q] for q in self.mine if k < q < j and q % self.Pr == r2)
+        r2 = self._rowof(j)
+        pos = sum(self.hgt[q] for q in self.mine if k < q < j and self._rowof(q) == r2)
         return self._bufs["col"][k % 2][r2][pos:pos + self.hgt[j]]
 
     def _update(self, j, k, which):
@@ -388,7 +404,7 @@ class BlockCyclicGP:
             ops.wait("gram", "panel")
             self._panel_factor(0)
         for k in range(nblk):
-            nxt_mine = k + 1 < nblk and (k + 1) % self.Pc == self.pc
+            nxt_mine = k + 1 < nblk and self._colof(k + 1) == self.pc
             with ops.on("panel"):
                 ops.wait("main_step_%d" % (k - 2), "panel")    # the buffers k % 2 were last read at step k - 2
                 self._distribute(k)
@@ -459,13 +475,13 @@ class BlockCyclicGP:
             # ---- forward
             for k in range(nblk):
                 w = self.hgt[k]
-                in_row, in_col = (k % self.Pr == self.pr), (k % self.Pc == self.pc)
+                in_row, in_col = (self._rowof(k) == self.pr), (self._colof(k) == self.pc)
                 diag = in_row and in_col
                 buf = msg[k % 2][:w]
                 if in_row:
                     part = acc[self.roff[k]:self.roff[k] + w]
                     if self.Pc > 1:
-                        dist.reduce(part, dst=self._grank(self.pr, k % self.Pc), group=self.row_group)
+                        dist.reduce(part, dst=self._grank(self.pr, self._colof(k)), group=self.row_group)
                         self.stats["collectives"] += 1
                     if diag:
                         torch.sub(y[k * nb:k * nb + w], part, out=buf)
@@ -474,7 +490,7 @@ class BlockCyclicGP:
                 if not in_col or k == nblk - 1:
                     continue
                 if self.Pr > 1:
-                    self._bcast(msg[k % 2], self._grank(k % self.Pr, self.pc), self.col_group)
+                    self._bcast(msg[k % 2], self._grank(self._rowof(k), self.pc), self.col_group)
                 o1, first = self._first_row_at_or_after(k + 1)
                 if first is not None:
                     off_k, _ = self._first_row_at_or_after(k)
@@ -482,7 +498,7 @@ class BlockCyclicGP:
             # ---- backward: acc now collects x_i for the owned rows
             for k in range(nblk - 1, -1, -1):
                 w = self.hgt[k]
-                in_row, in_col = (k % self.Pr == self.pr), (k % self.Pc == self.pc)
+                in_row, in_col = (self._rowof(k) == self.pr), (self._colof(k) == self.pc)
                 diag = in_row and in_col
                 buf = msg[k % 2][:w]
                 if in_col:
@@ -493,14 +509,14 @@ class BlockCyclicGP:
                     else:
                         buf.zero_()
                     if self.Pr > 1:
-                        dist.reduce(msg[k % 2], dst=self._grank(k % self.Pr, self.pc), group=self.col_group)
+                        dist.reduce(msg[k % 2], dst=self._grank(self._rowof(k), self.pc), group=self.col_group)
                         self.stats["collectives"] += 1
                     if diag:
                         torch.sub(zown[k], buf, out=buf)
                         ops.trsm(self.cols[k][:w, :w], self.invl[k], buf, True)
                 if in_row:
                     if self.Pc > 1:
-                        self._bcast(msg[k % 2], self._grank(self.pr, k % self.Pc), self.row_group)
+                        self._bcast(msg[k % 2], self._grank(self.pr, self._colof(k)), self.row_group)
                     acc[self.roff[k]:self.roff[k] + w].copy_(buf)
             # ---- every rank gets the whole alpha: each block row is contributed by grid column 0 of its grid row
             out = ops.zeros(self.N, ld)

@@ -25,7 +25,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, N, nb, M, kname, out, grid=None):
+def _worker(rank, world, port, N, nb, M, kname, out, grid=None, mirror=(False, False)):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -35,8 +35,17 @@ def _worker(rank, world, port, N, nb, M, kname, out, grid=None):
         from oracle import gpr_oracle as orc
         X, Y = make_problem(N, 3, M, seed=11)
         ops = CpuOps(KERNELS[kname], X, 1.0)
-        gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid)
-        if grid is None:
+        gp = gd.BlockCyclicGP(ops, N, nb=nb, grid=grid, mirror_rows=mirror[0], mirror_cols=mirror[1])
+        if any(mirror):    # mirrored maps: every lower block still has exactly one owner (checked over all ranks below)
+            owned = torch.zeros(gp.nblk, gp.nblk, dtype=torch.int64)
+            for j in gp.mine:
+                for i in gp.myrows:
+                    owned[i, j] = 1
+            dist.all_reduce(owned)
+            assert bool((owned == 1).all())
+            if mirror[0] and grid[0] > 1:   # 0 1 .. P-1 P-1 .. 1 0
+                assert [gp._rowof(i) for i in range(2 * grid[0])] == list(range(grid[0])) + list(range(grid[0] - 1, -1, -1))
+        elif grid is None:
             assert gp.mine == list(range(rank, gp.nblk, world))
         else:   # every block (i, j), i >= j, has exactly one owner and this rank holds exactly its own
             pr, pc = divmod(rank, grid[1])
@@ -91,6 +100,21 @@ def test_block_cyclic_learn_matches_oracle(tmp_path, world, N, nb, M, kname):
 def test_two_dimensional_grid_matches_oracle(tmp_path, world, grid, N, nb, M, kname):
     out = str(tmp_path / "res.pt")
     mp.spawn(_worker, args=(world, _free_port(), N, nb, M, kname, out, grid), nprocs=world, join=True)
+    res = torch.load(out)
+    assert res["err"] <= 1e-9, res
+    assert res["logdet_err"] <= 1e-10, res
+    assert res["same_alpha"] and res["relearn_same"]
+    assert res["potrf_streams"] == ["panel"] and not res["main_has_potrf"]
+
+
+@pytest.mark.parametrize("world,grid,mirror,N,nb,M,kname", [
+    (2, (2, 1), (True, False), 1100, 128, 2, "sum3"),      # the default map of libgprb200_dist.so on two GPUs
+    (4, (2, 2), (True, True), 1001, 128, 3, "prod"),       # both maps mirrored (consecutive block rows / panels on the same
+                                                           # grid row / column), ragged and odd last block
+])
+def test_mirrored_block_maps_match_oracle(tmp_path, world, grid, mirror, N, nb, M, kname):
+    out = str(tmp_path / "res.pt")
+    mp.spawn(_worker, args=(world, _free_port(), N, nb, M, kname, out, grid, mirror), nprocs=world, join=True)
     res = torch.load(out)
     assert res["err"] <= 1e-9, res
     assert res["logdet_err"] <= 1e-10, res
