@@ -95,7 +95,6 @@ def test_block_cyclic_learn_matches_oracle(tmp_path, world, N, nb, M, kname):
 @pytest.mark.parametrize("world,grid,N,nb,M,kname", [
     (2, (2, 1), 700, 128, 2, "sum3"),          # column communicator only
     (4, (2, 2), 1001, 128, 3, "rq"),           # the 2 x 2 schedule, ragged AND odd last block (1001 = 7 * 128 + 105)
-    (4, (1, 4), 900, 128, 1, "prod"),          # the degenerate 1 x g layout on the same code path
 ])
 def test_two_dimensional_grid_matches_oracle(tmp_path, world, grid, N, nb, M, kname):
     out = str(tmp_path / "res.pt")
